@@ -1,0 +1,188 @@
+/*
+ * yoda_b200.h -- C ABI of the B200-native Yoda Filter/Score hot path (libyoda_b200.so).
+ *
+ * This is the drop-in boundary: plain C types, opaque handle, no C++/torch types.  It is what
+ * a cgo shim inside the reference's pkg/yoda binds.  Every entry point
+ * cites the reference interface it replaces; paths are relative to the reference checkout
+ * (github.com/NJUPT-ISL/Yoda-Scheduler).
+ *
+ * Conventions
+ *   - every function returns YODA_OK (0) or a negative YODA_E_* code and never aborts or
+ *     throws; yoda_last_error() gives the thread-local message of the last failure.
+ *   - the library owns all device memory and its pinned staging memory; caller buffers are
+ *     read/written only during the call (cgo rule: no caller pointer is retained).
+ *   - one mutex per context: upsert/commit/eval calls on one context are serialised.
+ *   - there is NO CPU fallback: without a usable CUDA device yoda_create fails.
+ *   - node indices are dense, caller-assigned (node name <-> index lives on the host side).
+ */
+#ifndef YODA_B200_H
+#define YODA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YODA_ABI_VERSION 1
+#define YODA_MAX_CARDS 8 /* cards per node held in the device snapshot (len(Status.CardList) <= 8) */
+
+/* error codes */
+#define YODA_OK 0
+#define YODA_E_ARG (-1)    /* bad argument */
+#define YODA_E_CUDA (-2)   /* CUDA runtime error (message has the CUDA string) */
+#define YODA_E_RANGE (-3)  /* index / size outside the configured capacity */
+#define YODA_E_NOMEM (-4)  /* allocation failed */
+#define YODA_E_STATE (-5)  /* call order violated (e.g. eval with uncommitted flushed upserts) */
+#define YODA_E_DIV0 (-6)   /* TotalMemorySum == 0: the reference would panic (algorithm.go:71,86) */
+#define YODA_E_NCCL (-7)   /* NCCL unavailable or failed */
+
+typedef struct yoda_ctx yoda_ctx;
+
+typedef struct {
+    int32_t device;       /* CUDA device ordinal */
+    uint32_t max_nodes;   /* capacity of this context's (shard of the) snapshot */
+    uint32_t node_base;   /* global index of local node 0 (node-sharded configs, else 0) */
+    uint32_t shard_rank;  /* this shard's rank, 0 when unsharded */
+    uint32_t shard_count; /* number of node shards, 1 when unsharded */
+    uint32_t flags;       /* reserved, 0 */
+} yoda_config;
+
+/* One node's SCV object: the fields of scv.Scv / scv.Card the hot path reads (SURVEY.md 8(a) T1;
+ * call sites filter.go:13-58, collection.go:46-77, algorithm.go:58-86).  Arrays are indexed by
+ * position in Status.CardList.  healthy_mask bit g = (CardList[g].Health == "Healthy"). */
+typedef struct {
+    uint64_t card_number;      /* Status.CardNumber (independent of n_cards) */
+    uint64_t free_memory_sum;  /* Status.FreeMemorySum */
+    uint64_t total_memory_sum; /* Status.TotalMemorySum, must be > 0 */
+    uint32_t n_cards;          /* len(Status.CardList), <= YODA_MAX_CARDS */
+    uint32_t healthy_mask;
+    uint64_t free_memory[YODA_MAX_CARDS];
+    uint64_t total_memory[YODA_MAX_CARDS];
+    uint64_t clock[YODA_MAX_CARDS];
+    uint64_t core[YODA_MAX_CARDS];
+    uint64_t bandwidth[YODA_MAX_CARDS];
+    uint64_t power[YODA_MAX_CARDS];
+} yoda_node_record;
+
+/* One pending pod's requirement vector: its scv/number, scv/memory, scv/clock labels after
+ * strconv.Atoi-with-error-to-zero (filter.go:60-74; use yoda_parse_label).  32 bytes. */
+#define YODA_POD_HAS_NUMBER 1u
+#define YODA_POD_HAS_MEMORY 2u
+#define YODA_POD_HAS_CLOCK 4u
+typedef struct {
+    uint32_t flags; /* YODA_POD_HAS_*: label present in pod.GetLabels() */
+    uint32_t reserved;
+    uint64_t number, memory, clock;
+} yoda_pod_req;
+
+/* Per-pod outcome of one scheduling cycle.  72 bytes. */
+typedef struct {
+    /* collection.MaxValue in its declaration order (collection.go:14-21) */
+    uint64_t max_bandwidth, max_clock, max_core, max_free_memory, max_power, max_total_memory;
+    int64_t lowest, highest; /* as used by the rescale at scheduler.go:152 (after lowest--) */
+    uint32_t feasible;       /* number of nodes that passed Filter (all shards) */
+    int32_t chosen;          /* global index of the lowest-index node with the top score, -1 if none */
+} yoda_pod_result;
+
+/* eval flags */
+#define YODA_EVAL_DECIDE 0u       /* per-pod results only */
+#define YODA_EVAL_FULL 1u         /* also materialise feasible bits, raw and normalized scores in HBM */
+#define YODA_EVAL_FORCE_DIRECT 2u /* use the exact-u64 direct kernels even when the narrow path applies */
+
+/* rows of the device-resident result matrices (YODA_EVAL_FULL) */
+#define YODA_ROW_FEASIBLE_BITS 0 /* uint32 words, bit (n & 31) of word n >> 5 = node n passed Filter */
+#define YODA_ROW_RAW 1           /* int64 per node: what Yoda.Score returns (0 for nodes without SCV) */
+#define YODA_ROW_NORM 2          /* uint8 per node: NormalizeScore output, 0 for infeasible nodes */
+
+/* Device time of the phases of the last eval (CUDA events on the context's stream), ms. */
+typedef struct {
+    float total_ms;     /* first kernel -> last kernel, copies excluded */
+    float prep_ms;      /* pod canonicalisation, ordering, class tables */
+    float max_ms;       /* collection.CollectMaxValues */
+    float score_ms;     /* Filter+Score reduce (lowest/highest) */
+    float write_ms;     /* Filter+Score+NormalizeScore output pass (node choice) */
+    float h2d_ms, d2h_ms;
+    uint32_t kernels;   /* kernels launched by the last eval */
+    uint32_t path;      /* 0 = direct exact-u64, 1 = narrow fast path */
+    uint32_t n_classes; /* distinct score-divisor tuples in the batch (fast path) */
+    uint32_t n_groups;  /* distinct (clock, number, has-memory) requirement groups (fast path) */
+} yoda_timing;
+
+/* ---- lifecycle: replaces yoda.New's cache construction (pkg/yoda/scheduler.go:46-74) ---- */
+int yoda_create(const yoda_config *cfg, yoda_ctx **out);
+void yoda_destroy(yoda_ctx *ctx);
+int yoda_abi_version(void);
+const char *yoda_last_error(void);
+
+/* ---- snapshot maintenance: replaces the controller-runtime informer cache reads
+ *      y.cache.Get / y.cache.List (scheduler.go:80,98,118).  Called from Scv add/update/delete
+ *      and Pod add/delete event handlers.  Upserts are staged in pinned memory and become
+ *      visible to evaluations at the next yoda_commit. ---- */
+int yoda_node_upsert(yoda_ctx *ctx, uint32_t idx, const yoda_node_record *rec);
+int yoda_node_upsert_many(yoda_ctx *ctx, uint32_t n, const uint32_t *idx, const yoda_node_record *recs);
+/* sum of StrToUint64(scv/memory) over the pods running on the node (algorithm.go:75-80) */
+int yoda_node_set_alloc(yoda_ctx *ctx, uint32_t idx, uint64_t allocate_memory_sum);
+int yoda_node_set_alloc_many(yoda_ctx *ctx, uint32_t n, const uint32_t *idx, const uint64_t *allocate_memory_sum);
+/* Scv deleted: cache.Get fails -> node Unschedulable (scheduler.go:81-84) */
+int yoda_node_remove(yoda_ctx *ctx, uint32_t idx);
+int yoda_commit(yoda_ctx *ctx, uint64_t *epoch);
+int yoda_node_count(yoda_ctx *ctx, uint32_t *n_nodes); /* highest committed index + 1 */
+
+/* ---- evaluation: replaces, for a whole batch of pending pods on one frozen snapshot,
+ *      Yoda.Filter (scheduler.go:76-93) for every node, Yoda.PostFilter/CollectMaxValues
+ *      (scheduler.go:95-103, collection.go:30-57), Yoda.Score (scheduler.go:109-130) and
+ *      Yoda.NormalizeScore (scheduler.go:132-157), plus the lowest-index argmax. ---- */
+int yoda_eval_batch(yoda_ctx *ctx, const yoda_pod_req *pods, uint32_t n_pods, uint32_t flags, yoda_pod_result *out);
+/* same, with `d_pods` (n_pods * sizeof(yoda_pod_req)) and `d_out` (n_pods * sizeof(yoda_pod_result),
+ * may be NULL) already in device memory; asynchronous on the context's stream */
+int yoda_eval_batch_device(yoda_ctx *ctx, const void *d_pods, uint32_t n_pods, uint32_t flags, void *d_out);
+/* copy one row of the last YODA_EVAL_FULL result to the host: the O(1)-per-node memo behind
+ * later Filter/Score/NormalizeScore calls of the same cycle */
+int yoda_fetch_row(yoda_ctx *ctx, uint32_t pod, int kind, void *dst, size_t bytes);
+int yoda_sync(yoda_ctx *ctx);
+int yoda_last_timing(yoda_ctx *ctx, yoda_timing *t);
+/* device pointers of the last YODA_EVAL_FULL matrices (for zero-copy consumers); row strides in elements */
+int yoda_result_matrices(yoda_ctx *ctx, void **d_bits, void **d_raw, void **d_norm, uint64_t *stride_nodes);
+
+/* Yoda.NormalizeScore on an arbitrary score list, in place, on the device (scheduler.go:132-157):
+ * used when the framework's list is not Yoda's own feasible set (other plugins filtered too). */
+int yoda_normalize_scores(yoda_ctx *ctx, int64_t *scores, uint32_t n);
+
+/* filter.StrToUint64 / strToUint (filter.go:60-74): strconv.Atoi, any error -> 0 */
+uint64_t yoda_parse_label(const char *s, size_t len);
+/* filter.Uint64ToInt64 (filter.go:84-86): values >= 2^63 -> 0 */
+int64_t yoda_uint64_to_int64(uint64_t v);
+
+/* ---- node-sharded evaluation (BASELINE config 4): each shard holds nodes
+ *      [node_base, node_base + n) and sees every pod.  Either let the library reduce the
+ *      per-pod partials over NCCL (yoda_comm_*), or drive the phases yourself and reduce the
+ *      exchange buffers with any collective (yoda_phase_*). ---- */
+#define YODA_NCCL_ID_BYTES 128
+int yoda_comm_unique_id(void *id128);                                                    /* rank 0 */
+int yoda_comm_init(yoda_ctx *ctx, const void *id128, uint32_t rank, uint32_t n_ranks); /* all ranks */
+
+#define YODA_XCHG_MAX 0
+#define YODA_XCHG_SUM 1
+typedef struct {
+    void *d_ptr;    /* device pointer, uint64 elements */
+    uint64_t count; /* elements */
+    int32_t op;     /* YODA_XCHG_MAX / YODA_XCHG_SUM over shards, element-wise, unsigned */
+    int32_t reserved;
+} yoda_xchg;
+/* phases: 0 = upload pods + local maxima; 1 = local lowest/highest/count; 2 = local output pass
+ * and node choice; 3 = finish (write results).  After phases 0, 1 and 2 the buffers returned by
+ * yoda_phase_exchange must be reduced across shards before the next phase runs. */
+int yoda_phase_begin(yoda_ctx *ctx, const yoda_pod_req *pods, uint32_t n_pods, uint32_t flags);
+int yoda_phase_run(yoda_ctx *ctx, int phase);
+int yoda_phase_exchange(yoda_ctx *ctx, int phase, yoda_xchg *bufs, int *n_bufs /* in: capacity, out: used */);
+int yoda_phase_finish(yoda_ctx *ctx, yoda_pod_result *out);
+
+/* run subsequent work of this context on the caller's CUDA stream (cudaStream_t), NULL = own stream */
+int yoda_set_stream(yoda_ctx *ctx, void *cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YODA_B200_H */

@@ -1,0 +1,208 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle -- bit exact."""
+import random
+
+import numpy as np
+import pytest
+from conftest import kat_nodes
+
+from oracle import oracle as ora
+from parity import assert_matches_oracle, gpu_cycle, norm_as_u8
+from test_oracle_kat import random_nodes, random_pods
+from yoda_scheduler_b200 import api, synth
+from yoda_scheduler_b200.labels import pods_to_requests
+from yoda_scheduler_b200.snapshot import Snapshot
+
+pytestmark = pytest.mark.gpu
+
+PATHS = [api.EVAL_FULL, api.EVAL_FULL | api.EVAL_FORCE_DIRECT]
+
+
+@pytest.mark.parametrize("flags", PATHS)
+def test_kat_through_c_abi(kat, flags):
+    nodes = kat_nodes(kat)
+    snap = Snapshot.from_nodes(nodes)
+    names = [n["name"] for n in kat["nodes"]]
+    labels = [c["labels"] for c in kat["cases"]]
+    res, mats, _ = gpu_cycle(snap, pods_to_requests(labels), flags)
+    for p, case in enumerate(kat["cases"]):
+        feas = [1 if nm in case["feasible"] else 0 for nm in names]
+        assert mats["feasible"][p].tolist() == feas
+        got_max = [int(res[k][p]) for k in ("max_bandwidth", "max_clock", "max_core", "max_free_memory", "max_power", "max_total_memory")]
+        assert got_max == case["max6"]
+        for n, nm in enumerate(names):
+            if feas[n]:
+                assert mats["raw"][p, n] == case["raw"][nm]
+                assert mats["norm"][p, n] == case["norm"][nm]
+        assert res["chosen"][p] == (-1 if case["chosen"] is None else names.index(case["chosen"]))
+    assert_matches_oracle(snap, labels, res, mats)
+
+
+@pytest.mark.parametrize("flags", PATHS)
+@pytest.mark.parametrize("adversarial", [False, True])
+@pytest.mark.parametrize("seed", range(8))
+def test_random_small(seed, adversarial, flags):
+    rng = random.Random(77 * seed + adversarial)
+    nodes = random_nodes(rng, rng.choice([1, 3, 31, 32, 33, 127, 129, 300]), adversarial)
+    labels = random_pods(rng, rng.choice([1, 2, 17, 129, 400]), adversarial)
+    snap = Snapshot.from_nodes(nodes)
+    res, mats, _ = gpu_cycle(snap, pods_to_requests(labels), flags)
+    assert_matches_oracle(snap, labels, res, mats, what=f"seed={seed} adv={adversarial}")
+
+
+@pytest.mark.parametrize("flags", PATHS)
+def test_config_c1(flags):
+    """BASELINE config 1: 100 nodes x 8 cards, one pod scv/memory=1000."""
+    snap = synth.make_snapshot(100)
+    labels = [{"scv/memory": "1000"}]
+    res, mats, _ = gpu_cycle(snap, pods_to_requests(labels), flags)
+    assert_matches_oracle(snap, labels, res, mats)
+    assert res["chosen"][0] >= 0
+
+
+@pytest.mark.parametrize("flags", PATHS)
+def test_config_c2(flags):
+    """BASELINE config 2: 5k nodes, 1k pods with mixed labels."""
+    n, p, seed = synth.CONFIGS["c2"]
+    snap = synth.make_snapshot(n)
+    labels = synth.make_pod_labels(p, seed)
+    reqs = synth.make_requests(p, seed)
+    assert np.array_equal(reqs, pods_to_requests(labels))
+    res, mats, _ = gpu_cycle(snap, reqs, flags)
+    assert_matches_oracle(snap, labels, res, mats)
+
+
+def test_decide_mode_equals_full():
+    n, p, seed = synth.CONFIGS["c2"]
+    snap = synth.make_snapshot(n)
+    reqs = synth.make_requests(p, seed)
+    full, _, _ = gpu_cycle(snap, reqs, api.EVAL_FULL, fetch=False)
+    dec, _, _ = gpu_cycle(snap, reqs, api.EVAL_DECIDE)
+    assert np.array_equal(full, dec)
+
+
+def test_config_c3_subsample():
+    """BASELINE config 3 shape (50k nodes), a 1536-pod slice of the 100k batch, against the oracle."""
+    n, p, seed = synth.CONFIGS["c3"]
+    snap = synth.make_snapshot(n)
+    labels = synth.make_pod_labels(p, seed)[:1536]
+    reqs = synth.make_requests(p, seed)[:1536]
+    res, mats, _ = gpu_cycle(snap, reqs, api.EVAL_FULL)
+    assert_matches_oracle(snap, labels, res, mats)
+
+
+def test_empty_and_degenerate():
+    snap = synth.make_snapshot(64)
+    with api.Context(64) as ctx:
+        ctx.load_snapshot(snap)
+        assert len(ctx.eval(np.zeros(0, api.POD_REQ))) == 0          # empty batch
+    # snapshot in which no node has an SCV: nothing is feasible
+    s2 = synth.make_snapshot(40)
+    s2.has_scv[:] = 0
+    labels = [{}, {"scv/memory": "1"}]
+    res, mats, _ = gpu_cycle(s2, pods_to_requests(labels))
+    assert res["chosen"].tolist() == [-1, -1] and res["feasible"].tolist() == [0, 0]
+    assert_matches_oracle(s2, labels, res, mats)
+    # a context that never saw a node
+    with api.Context(8) as ctx:
+        ctx.commit()
+        r = ctx.eval(pods_to_requests([{}]), api.EVAL_DECIDE)
+        assert r["chosen"][0] == -1 and r["max_core"][0] == 1
+
+
+def test_incremental_upserts_equal_full_rebuild():
+    """Churn (BASELINE config 5 shape, small): 10% of the nodes change per tick; the incrementally
+    maintained device snapshot must answer exactly like one rebuilt from scratch."""
+    rng = np.random.default_rng(5)
+    N, P = 3000, 300
+    snap = synth.make_snapshot(N)
+    reqs = synth.make_requests(P, synth.SEED + 5)
+    labels = synth.make_pod_labels(P, synth.SEED + 5)
+    with api.Context(N) as inc:
+        inc.load_snapshot(snap)
+        for tick in range(3):
+            touched = rng.choice(N, N // 10, replace=False)
+            other = synth.make_snapshot(N, seed=synth.SEED + 100 + tick)
+            for f in ("free_memory", "healthy_mask", "free_memory_sum"):
+                getattr(snap, f)[touched] = getattr(other, f)[touched]
+            gone = touched[:5]
+            snap.has_scv[gone] = 0
+            back = touched[5:10]
+            snap.has_scv[back] = 1
+            alloc = snap.alloc_sum()
+            alloc[touched[10:60]] += np.uint64(1024)
+            live = touched[snap.has_scv[touched] == 1]
+            inc.upsert_many(live, snap.records(live))
+            for i in gone:
+                inc.remove(int(i))
+            inc.set_alloc_many(touched[10:60], alloc[touched[10:60]])
+            # eval with staged-but-uncommitted updates is refused
+            with pytest.raises(api.YodaError) as e:
+                inc.eval(reqs)
+            assert e.value.code == -5
+            inc.commit()
+            r_inc = inc.eval(reqs)
+            m_inc = inc.fetch_all(P)
+            with api.Context(N) as full:
+                full.load_snapshot(snap, commit=False)
+                full.set_alloc_many(np.arange(N), alloc)
+                full.commit()
+                r_full = full.eval(reqs)
+                m_full = full.fetch_all(P)
+            assert np.array_equal(r_inc, r_full)
+            for k in m_inc:
+                assert np.array_equal(m_inc[k], m_full[k]), k
+            # fold the extra allocations into the host mirror so the oracle sees them too
+            extra = np.zeros(N, np.uint64)
+            extra[touched[10:60]] = 1024
+            counts = np.diff(snap.pod_off).astype(np.int64)
+            add = extra > 0
+            new_mem, new_off = [], [0]
+            for i in range(N):
+                seg = list(snap.pod_mem[snap.pod_off[i]:snap.pod_off[i + 1]])
+                if add[i]:
+                    seg.append(1024)
+                new_mem += seg
+                new_off.append(len(new_mem))
+            snap.pod_mem = np.array(new_mem, np.uint64)
+            snap.pod_off = np.array(new_off, np.uint32)
+            assert_matches_oracle(snap, labels, r_inc, m_inc, what=f"tick {tick}")
+
+
+def test_normalize_scores_on_device(kat):
+    with api.Context(4) as ctx:
+        for src, want in kat["normalize"]:
+            assert ctx.normalize_scores(src).tolist() == want
+        rng = np.random.default_rng(0)
+        for hi in (50, 2**40, 2**62):
+            a = rng.integers(-hi, hi, 5000, dtype=np.int64)
+            assert ctx.normalize_scores(a).tolist() == ora.normalize_score(a.tolist())
+        with pytest.raises(api.YodaError):
+            ctx.normalize_scores([])
+
+
+def test_upsert_validation():
+    with api.Context(4) as ctx:
+        rec = np.zeros(1, api.NODE_REC)
+        rec["total_memory_sum"] = 0
+        with pytest.raises(api.YodaError) as e:
+            ctx.upsert(0, rec)
+        assert e.value.code == -6                      # reference would panic: algorithm.go:71
+        rec["total_memory_sum"] = 1
+        rec["n_cards"] = 9
+        with pytest.raises(api.YodaError) as e:
+            ctx.upsert(0, rec)
+        assert e.value.code == -3
+        rec["n_cards"] = 1
+        with pytest.raises(api.YodaError) as e:
+            ctx.upsert(4, rec)
+        assert e.value.code == -3
+
+
+def test_staging_ring_overflow_is_safe():
+    """More pending upserts than the pinned ring holds: early flushes, still exact after commit."""
+    N = 70000  # ring capacity is 65536 records
+    snap = synth.make_snapshot(N)
+    reqs = synth.make_requests(64, 9)
+    labels = synth.make_pod_labels(64, 9)
+    res, mats, _ = gpu_cycle(snap, reqs)
+    assert_matches_oracle(snap, labels, res, mats)

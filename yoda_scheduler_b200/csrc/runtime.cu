@@ -1,0 +1,813 @@
+// runtime.cu -- host runtime behind the C ABI of include/yoda_b200.h:
+// device snapshot, pinned update staging, eval workspace, phase driver, NCCL exchange.
+#include <dlfcn.h>
+#include <nccl.h>  // types only; the library is dlopen'ed on demand (yoda_comm_*)
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "direct_kernels.cuh"
+
+// ------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CU(x)                                                                                              \
+    do {                                                                                                   \
+        cudaError_t e_ = (x);                                                                              \
+        if (e_ != cudaSuccess) return fail(YODA_E_CUDA, "%s failed: %s (%s:%d)", #x, cudaGetErrorString(e_), \
+                                           __FILE__, __LINE__);                                            \
+    } while (0)
+#define TRY(x)              \
+    do {                    \
+        int rc_ = (x);      \
+        if (rc_) return rc_; \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------
+// NCCL through dlopen (the library must load and run on one GPU without NCCL present)
+// ------------------------------------------------------------------------------------------
+struct NcclApi {
+    void *h = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi g_nccl;
+static std::mutex g_nccl_mu;
+static int nccl_load() {
+    std::lock_guard<std::mutex> lk(g_nccl_mu);
+    if (g_nccl.h) return YODA_OK;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return fail(YODA_E_NCCL, "cannot dlopen libnccl.so.2: %s", dlerror());
+#define SYM(n)                                                         \
+    *(void **)(&g_nccl.n) = dlsym(h, "nccl" #n);                       \
+    if (!g_nccl.n) return fail(YODA_E_NCCL, "nccl" #n " not found in libnccl")
+    SYM(GetUniqueId);
+    SYM(CommInitRank);
+    SYM(AllReduce);
+    SYM(GroupStart);
+    SYM(GroupEnd);
+    SYM(CommDestroy);
+    SYM(GetErrorString);
+#undef SYM
+    g_nccl.h = h;
+    return YODA_OK;
+}
+#define NC(x)                                                                                      \
+    do {                                                                                           \
+        ncclResult_t r_ = (x);                                                                     \
+        if (r_ != ncclSuccess) return fail(YODA_E_NCCL, "%s failed: %s", #x, g_nccl.GetErrorString(r_)); \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------
+enum { EV_START = 0, EV_PREP, EV_MAX, EV_SCORE, EV_WRITE, EV_H2D0, EV_H2D1, EV_D2H0, EV_D2H1, EV_COUNT };
+
+struct yoda_ctx {
+    std::mutex mu;
+    yoda_config cfg{};
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    DevSnap snap{};
+    u32 *d_wide_flag = nullptr;
+    bool narrow_ok = false;
+    uint64_t epoch = 0;
+    // update staging
+    UpdRec *h_upd = nullptr, *d_upd = nullptr;
+    u32 upd_cap = 0, n_upd = 0;
+    std::vector<int32_t> slot_of;
+    bool flushed_uncommitted = false;
+    u32 n_nodes_pending = 0;
+    // eval workspace
+    u32 pods_cap = 0;
+    yoda_pod_req *d_req = nullptr, *h_req = nullptr;
+    PodC *d_pods = nullptr;
+    u64 *d_max6 = nullptr, *d_count = nullptr, *d_hilo = nullptr, *d_ckey = nullptr;
+    yoda_pod_result *d_res = nullptr, *h_res = nullptr;
+    // result matrices
+    size_t raw_cap = 0, bits_cap = 0;
+    i64 *d_raw = nullptr;
+    u8 *d_norm = nullptr;
+    u32 *d_bits = nullptr;
+    u64 stride = 0;
+    u32 last_P = 0;
+    bool last_full = false;
+    // phase state
+    u32 ph_P = 0, ph_flags = 0;
+    int ph_done = -1;
+    const yoda_pod_req *ph_dev_req = nullptr;
+    // timing
+    cudaEvent_t ev[EV_COUNT]{};
+    yoda_timing timing{};
+    u32 launches = 0;
+    // NormalizeScore list scratch
+    i64 *d_list = nullptr, *d_lohi = nullptr;
+    u32 list_cap = 0;
+    // NCCL
+    ncclComm_t comm = nullptr;
+};
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) ok = (cudaSetDevice(dev) == cudaSuccess);
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+template <typename T>
+static int dev_alloc(T **p, size_t n) {
+    void *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T));
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(YODA_E_NOMEM, "cudaMalloc of %zu bytes failed: %s", n * sizeof(T), cudaGetErrorString(e));
+    }
+    *p = (T *)q;
+    return YODA_OK;
+}
+template <typename T>
+static void dev_free(T *&p) {
+    if (p) cudaFree(p);
+    p = nullptr;
+}
+
+static u32 round_up(u32 x, u32 m) { return (x + m - 1) / m * m; }
+
+extern "C" int yoda_abi_version(void) { return YODA_ABI_VERSION; }
+extern "C" const char *yoda_last_error(void) { return g_err; }
+
+extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
+    if (!cfg || !out) return fail(YODA_E_ARG, "yoda_create: null argument");
+    if (cfg->max_nodes == 0) return fail(YODA_E_ARG, "yoda_create: max_nodes must be > 0");
+    if (cfg->shard_count == 0 || cfg->shard_rank >= cfg->shard_count)
+        return fail(YODA_E_ARG, "yoda_create: bad shard rank/count %u/%u", cfg->shard_rank, cfg->shard_count);
+    if ((uint64_t)cfg->node_base + cfg->max_nodes > 0xFFFFFFFEull)
+        return fail(YODA_E_RANGE, "yoda_create: node_base + max_nodes exceeds 2^32-2");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(YODA_E_CUDA, "no usable CUDA device (%s); this library has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(YODA_E_ARG, "yoda_create: device %d of %d", cfg->device, ndev);
+    DeviceGuard dg(cfg->device);
+    if (!dg.ok) return fail(YODA_E_CUDA, "cudaSetDevice(%d) failed", cfg->device);
+    yoda_ctx *c = new (std::nothrow) yoda_ctx();
+    if (!c) return fail(YODA_E_NOMEM, "out of host memory");
+    c->cfg = *cfg;
+    auto bail = [&](int rc) {
+        yoda_destroy(c);
+        return rc;
+    };
+    if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess)
+        return bail(fail(YODA_E_CUDA, "cudaStreamCreate failed"));
+    c->stream = c->own_stream;
+    for (int i = 0; i < EV_COUNT; ++i)
+        if (cudaEventCreate(&c->ev[i]) != cudaSuccess) return bail(fail(YODA_E_CUDA, "cudaEventCreate failed"));
+    const u32 cap = round_up(cfg->max_nodes, 128);
+    DevSnap &s = c->snap;
+    s.cap = cap;
+    s.n_nodes = 0;
+    s.node_base = cfg->node_base;
+    int rc = 0;
+    for (int f = 0; f < NFIELD && !rc; ++f) rc = dev_alloc(&s.f[f], (size_t)cap * G);
+    if (!rc) rc = dev_alloc(&s.card_number, cap);
+    if (!rc) rc = dev_alloc(&s.free_sum, cap);
+    if (!rc) rc = dev_alloc(&s.total_sum, cap);
+    if (!rc) rc = dev_alloc(&s.alloc_sum, cap);
+    if (!rc) rc = dev_alloc(&s.stat, cap);
+    if (!rc) rc = dev_alloc(&s.meta, cap);
+    if (!rc) rc = dev_alloc(&s.free32, (size_t)cap * G);
+    if (!rc) rc = dev_alloc(&s.clock32, (size_t)cap * G);
+    if (!rc) rc = dev_alloc(&s.cardnum32, cap);
+    if (!rc) rc = dev_alloc(&s.stat32, cap);
+    if (!rc) rc = dev_alloc(&c->d_wide_flag, 1);
+    if (!rc) rc = dev_alloc(&c->d_lohi, 2);
+    if (rc) return bail(rc);
+    for (int f = 0; f < NFIELD; ++f) cudaMemsetAsync(s.f[f], 0, (size_t)cap * G * 8, c->stream);
+    cudaMemsetAsync(s.card_number, 0, (size_t)cap * 8, c->stream);
+    cudaMemsetAsync(s.free_sum, 0, (size_t)cap * 8, c->stream);
+    cudaMemsetAsync(s.total_sum, 0, (size_t)cap * 8, c->stream);
+    cudaMemsetAsync(s.alloc_sum, 0, (size_t)cap * 8, c->stream);
+    cudaMemsetAsync(s.stat, 0, (size_t)cap * 8, c->stream);
+    cudaMemsetAsync(s.meta, 0, (size_t)cap * 4, c->stream);
+    c->upd_cap = std::min<u32>(cfg->max_nodes, 1u << 16);
+    if (cudaMallocHost((void **)&c->h_upd, (size_t)c->upd_cap * sizeof(UpdRec)) != cudaSuccess)
+        return bail(fail(YODA_E_NOMEM, "cudaMallocHost of the update staging buffer failed"));
+    rc = dev_alloc(&c->d_upd, c->upd_cap);
+    if (rc) return bail(rc);
+    c->slot_of.assign(cfg->max_nodes, -1);
+    if (cudaStreamSynchronize(c->stream) != cudaSuccess) return bail(fail(YODA_E_CUDA, "initial memset failed"));
+    *out = c;
+    return YODA_OK;
+}
+
+extern "C" void yoda_destroy(yoda_ctx *c) {
+    if (!c) return;
+    DeviceGuard dg(c->cfg.device);
+    cudaDeviceSynchronize();
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    DevSnap &s = c->snap;
+    for (int f = 0; f < NFIELD; ++f) dev_free(s.f[f]);
+    dev_free(s.card_number); dev_free(s.free_sum); dev_free(s.total_sum); dev_free(s.alloc_sum);
+    dev_free(s.stat); dev_free(s.meta); dev_free(s.free32); dev_free(s.clock32);
+    dev_free(s.cardnum32); dev_free(s.stat32);
+    dev_free(c->d_wide_flag); dev_free(c->d_lohi); dev_free(c->d_list); dev_free(c->d_upd);
+    dev_free(c->d_req); dev_free(c->d_pods); dev_free(c->d_max6); dev_free(c->d_count);
+    dev_free(c->d_hilo); dev_free(c->d_ckey); dev_free(c->d_res);
+    dev_free(c->d_raw); dev_free(c->d_norm); dev_free(c->d_bits);
+    if (c->h_upd) cudaFreeHost(c->h_upd);
+    if (c->h_req) cudaFreeHost(c->h_req);
+    if (c->h_res) cudaFreeHost(c->h_res);
+    for (int i = 0; i < EV_COUNT; ++i)
+        if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+extern "C" int yoda_set_stream(yoda_ctx *c, void *cuda_stream) {
+    if (!c) return fail(YODA_E_ARG, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    CU(cudaStreamSynchronize(c->stream));
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return YODA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// snapshot maintenance
+// ------------------------------------------------------------------------------------------
+static int flush_updates(yoda_ctx *c) {
+    if (c->n_upd == 0) return YODA_OK;
+    CU(cudaMemcpyAsync(c->d_upd, c->h_upd, (size_t)c->n_upd * sizeof(UpdRec), cudaMemcpyHostToDevice, c->stream));
+    const u32 threads = c->n_upd * G;
+    k_scatter_updates<<<(threads + 255) / 256, 256, 0, c->stream>>>(c->snap, c->d_upd, c->n_upd);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(c->stream));  // the pinned buffer is reused right away
+    for (u32 i = 0; i < c->n_upd; ++i) c->slot_of[c->h_upd[i].idx] = -1;
+    c->n_upd = 0;
+    return YODA_OK;
+}
+
+static int stage_slot(yoda_ctx *c, u32 idx, UpdRec **out) {
+    if (idx >= c->cfg.max_nodes) return fail(YODA_E_RANGE, "node index %u >= max_nodes %u", idx, c->cfg.max_nodes);
+    int32_t sl = c->slot_of[idx];
+    if (sl < 0) {
+        if (c->n_upd == c->upd_cap) {
+            TRY(flush_updates(c));
+            c->flushed_uncommitted = true;
+        }
+        sl = (int32_t)c->n_upd++;
+        c->slot_of[idx] = sl;
+        c->h_upd[sl].idx = idx;
+        c->h_upd[sl].op = 0;
+        c->h_upd[sl].alloc = 0;
+    }
+    c->n_nodes_pending = std::max(c->n_nodes_pending, idx + 1);
+    *out = &c->h_upd[sl];
+    return YODA_OK;
+}
+
+static int check_record(const yoda_node_record *r, u32 idx) {
+    if (r->n_cards > YODA_MAX_CARDS)
+        return fail(YODA_E_RANGE, "node %u: %u cards, the device snapshot holds at most %d per node", idx, r->n_cards,
+                    YODA_MAX_CARDS);
+    if (r->total_memory_sum == 0)
+        return fail(YODA_E_DIV0, "node %u: TotalMemorySum == 0 (the reference divides by it, algorithm.go:71,86)", idx);
+    return YODA_OK;
+}
+
+static int upsert_locked(yoda_ctx *c, u32 idx, const yoda_node_record *rec) {
+    TRY(check_record(rec, idx));
+    UpdRec *u;
+    TRY(stage_slot(c, idx, &u));
+    u->rec = *rec;
+    u->op = (u->op | UPD_REC) & ~UPD_REMOVE;
+    return YODA_OK;
+}
+
+extern "C" int yoda_node_upsert(yoda_ctx *c, u32 idx, const yoda_node_record *rec) {
+    if (!c || !rec) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    return upsert_locked(c, idx, rec);
+}
+
+extern "C" int yoda_node_upsert_many(yoda_ctx *c, u32 n, const u32 *idx, const yoda_node_record *recs) {
+    if (!c || (n && (!idx || !recs))) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    for (u32 i = 0; i < n; ++i) TRY(upsert_locked(c, idx[i], &recs[i]));
+    return YODA_OK;
+}
+
+extern "C" int yoda_node_set_alloc(yoda_ctx *c, u32 idx, uint64_t a) {
+    if (!c) return fail(YODA_E_ARG, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    UpdRec *u;
+    TRY(stage_slot(c, idx, &u));
+    u->alloc = a;
+    u->op |= UPD_ALLOC;
+    return YODA_OK;
+}
+
+extern "C" int yoda_node_set_alloc_many(yoda_ctx *c, u32 n, const u32 *idx, const uint64_t *a) {
+    if (!c || (n && (!idx || !a))) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    for (u32 i = 0; i < n; ++i) {
+        UpdRec *u;
+        TRY(stage_slot(c, idx[i], &u));
+        u->alloc = a[i];
+        u->op |= UPD_ALLOC;
+    }
+    return YODA_OK;
+}
+
+extern "C" int yoda_node_remove(yoda_ctx *c, u32 idx) {
+    if (!c) return fail(YODA_E_ARG, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    UpdRec *u;
+    TRY(stage_slot(c, idx, &u));
+    u->op = (u->op | UPD_REMOVE) & ~UPD_REC;
+    return YODA_OK;
+}
+
+extern "C" int yoda_commit(yoda_ctx *c, uint64_t *epoch) {
+    if (!c) return fail(YODA_E_ARG, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    TRY(flush_updates(c));
+    c->snap.n_nodes = c->n_nodes_pending;
+    c->flushed_uncommitted = false;
+    CU(cudaMemsetAsync(c->d_wide_flag, 0, sizeof(u32), c->stream));
+    if (c->snap.n_nodes) {
+        k_prepare<<<(c->snap.n_nodes + 255) / 256, 256, 0, c->stream>>>(c->snap, c->d_wide_flag);
+        CU(cudaGetLastError());
+    }
+    u32 wide = 0;
+    CU(cudaMemcpyAsync(&wide, c->d_wide_flag, sizeof(u32), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->narrow_ok = (wide == 0);
+    c->epoch++;
+    c->last_P = 0;  // result matrices belong to the previous snapshot
+    if (epoch) *epoch = c->epoch;
+    return YODA_OK;
+}
+
+extern "C" int yoda_node_count(yoda_ctx *c, u32 *n) {
+    if (!c || !n) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    *n = c->snap.n_nodes;
+    return YODA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// evaluation
+// ------------------------------------------------------------------------------------------
+static int ensure_pods(yoda_ctx *c, u32 P) {
+    if (P <= c->pods_cap) return YODA_OK;
+    const u32 cap = round_up(std::max(P, 1024u), 1024);
+    CU(cudaStreamSynchronize(c->stream));
+    dev_free(c->d_req); dev_free(c->d_pods); dev_free(c->d_max6); dev_free(c->d_count);
+    dev_free(c->d_hilo); dev_free(c->d_ckey); dev_free(c->d_res);
+    if (c->h_req) cudaFreeHost(c->h_req);
+    if (c->h_res) cudaFreeHost(c->h_res);
+    c->h_req = nullptr;
+    c->h_res = nullptr;
+    c->pods_cap = 0;
+    TRY(dev_alloc(&c->d_req, cap));
+    TRY(dev_alloc(&c->d_pods, cap));
+    TRY(dev_alloc(&c->d_max6, (size_t)cap * 6));
+    TRY(dev_alloc(&c->d_count, cap));
+    TRY(dev_alloc(&c->d_hilo, (size_t)cap * 2));
+    TRY(dev_alloc(&c->d_ckey, cap));
+    TRY(dev_alloc(&c->d_res, cap));
+    if (cudaMallocHost((void **)&c->h_req, (size_t)cap * sizeof(yoda_pod_req)) != cudaSuccess ||
+        cudaMallocHost((void **)&c->h_res, (size_t)cap * sizeof(yoda_pod_result)) != cudaSuccess)
+        return fail(YODA_E_NOMEM, "cudaMallocHost of the pod staging buffers failed");
+    c->pods_cap = cap;
+    return YODA_OK;
+}
+
+static int ensure_matrices(yoda_ctx *c, u32 P, u64 stride) {
+    const size_t need = (size_t)P * stride, need_bits = (size_t)P * (stride / 32);
+    if (need > c->raw_cap) {
+        CU(cudaStreamSynchronize(c->stream));
+        dev_free(c->d_raw);
+        dev_free(c->d_norm);
+        c->raw_cap = 0;
+        TRY(dev_alloc(&c->d_raw, need));
+        TRY(dev_alloc(&c->d_norm, need));
+        c->raw_cap = need;
+    }
+    if (need_bits > c->bits_cap) {
+        CU(cudaStreamSynchronize(c->stream));
+        dev_free(c->d_bits);
+        c->bits_cap = 0;
+        TRY(dev_alloc(&c->d_bits, need_bits));
+        c->bits_cap = need_bits;
+    }
+    return YODA_OK;
+}
+
+#define LAUNCHED(c)          \
+    do {                     \
+        CU(cudaGetLastError()); \
+        (c)->launches++;     \
+    } while (0)
+
+// phase 0: canonical pods, identities, local maxima + feasible counts
+static int phase0(yoda_ctx *c, const yoda_pod_req *d_req) {
+    const u32 P = c->ph_P, N = c->snap.n_nodes;
+    cudaStream_t st = c->stream;
+    c->launches = 0;
+    CU(cudaEventRecord(c->ev[EV_START], st));
+    k_pod_prep<<<(P + 255) / 256, 256, 0, st>>>(d_req, c->d_pods, P);
+    LAUNCHED(c);
+    k_init_partials<<<(P + 255) / 256, 256, 0, st>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, P);
+    LAUNCHED(c);
+    CU(cudaEventRecord(c->ev[EV_PREP], st));
+    if (N) {
+        const u32 gx = (P + DPT - 1) / DPT;
+        u32 chunks = std::max(1u, std::min((N + DTN - 1) / DTN, (592u + gx - 1) / gx));
+        chunks = std::min(chunks, 65535u);
+        const u32 npc = round_up((N + chunks - 1) / chunks, DTN);
+        dim3 grid(gx, (N + npc - 1) / npc);
+        k_direct_pods<0><<<grid, DPT, 0, st>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_count, c->d_hilo);
+        LAUNCHED(c);
+    }
+    CU(cudaEventRecord(c->ev[EV_MAX], st));
+    return YODA_OK;
+}
+
+// phase 1: local lowest/highest over feasible nodes
+static int phase1(yoda_ctx *c) {
+    const u32 P = c->ph_P, N = c->snap.n_nodes;
+    cudaStream_t st = c->stream;
+    if (N) {
+        const u32 gx = (P + DPT - 1) / DPT;
+        u32 chunks = std::max(1u, std::min((N + DTN - 1) / DTN, (592u + gx - 1) / gx));
+        chunks = std::min(chunks, 65535u);
+        const u32 npc = round_up((N + chunks - 1) / chunks, DTN);
+        dim3 grid(gx, (N + npc - 1) / npc);
+        k_direct_pods<1><<<grid, DPT, 0, st>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_count, c->d_hilo);
+        LAUNCHED(c);
+    }
+    CU(cudaEventRecord(c->ev[EV_SCORE], st));
+    return YODA_OK;
+}
+
+// phase 2: output pass (matrices when FULL) + node choice
+static int phase2(yoda_ctx *c) {
+    const u32 P = c->ph_P, N = c->snap.n_nodes;
+    cudaStream_t st = c->stream;
+    const bool full = (c->ph_flags & YODA_EVAL_FULL) != 0;
+    if (N) {
+        const u32 gx = (N + DCT - 1) / DCT;
+        const u32 want_y = std::max(1u, 2368u / gx);
+        u32 ppc = std::max(1u, (P + want_y - 1) / want_y);
+        ppc = std::min(ppc, 64u);
+        ppc = std::max(ppc, (P + 65534u) / 65535u);
+        dim3 grid(gx, (P + ppc - 1) / ppc);
+        if (full)
+            k_direct_out<true><<<grid, DCT, 0, st>>>(c->snap, c->d_pods, P, ppc, c->d_max6, c->d_count, c->d_hilo, c->d_ckey,
+                                                     c->d_raw, c->d_norm, c->d_bits, c->stride);
+        else
+            k_direct_out<false><<<grid, DCT, 0, st>>>(c->snap, c->d_pods, P, ppc, c->d_max6, c->d_count, c->d_hilo, c->d_ckey,
+                                                      nullptr, nullptr, nullptr, c->stride);
+        LAUNCHED(c);
+    }
+    return YODA_OK;
+}
+
+static int phase3(yoda_ctx *c) {
+    const u32 P = c->ph_P;
+    k_finalize<<<(P + 255) / 256, 256, 0, c->stream>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, c->d_res, P);
+    LAUNCHED(c);
+    CU(cudaEventRecord(c->ev[EV_WRITE], c->stream));
+    return YODA_OK;
+}
+
+static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
+    if (c->flushed_uncommitted || c->n_upd)
+        return fail(YODA_E_STATE, "uncommitted node updates are pending: call yoda_commit before evaluating");
+    TRY(ensure_pods(c, P));
+    c->stride = round_up(std::max(c->snap.n_nodes, 1u), 128);
+    if (flags & YODA_EVAL_FULL) TRY(ensure_matrices(c, P, c->stride));
+    c->ph_P = P;
+    c->ph_flags = flags;
+    c->ph_done = -1;
+    c->last_P = 0;
+    c->last_full = false;
+    return YODA_OK;
+}
+
+static int exchange_locked(yoda_ctx *c, int phase) {
+    if (!c->comm) return YODA_OK;
+    const u32 P = c->ph_P;
+    if (phase == 0) {
+        NC(g_nccl.GroupStart());
+        NC(g_nccl.AllReduce(c->d_max6, c->d_max6, (size_t)P * 6, ncclUint64, ncclMax, c->comm, c->stream));
+        NC(g_nccl.AllReduce(c->d_count, c->d_count, P, ncclUint64, ncclSum, c->comm, c->stream));
+        NC(g_nccl.GroupEnd());
+    } else if (phase == 1) {
+        NC(g_nccl.AllReduce(c->d_hilo, c->d_hilo, (size_t)P * 2, ncclUint64, ncclMax, c->comm, c->stream));
+    } else if (phase == 2) {
+        NC(g_nccl.AllReduce(c->d_ckey, c->d_ckey, P, ncclUint64, ncclMax, c->comm, c->stream));
+    }
+    return YODA_OK;
+}
+
+static void collect_timing(yoda_ctx *c, bool copies) {
+    yoda_timing &t = c->timing;
+    memset(&t, 0, sizeof t);
+    cudaEventElapsedTime(&t.total_ms, c->ev[EV_START], c->ev[EV_WRITE]);
+    cudaEventElapsedTime(&t.prep_ms, c->ev[EV_START], c->ev[EV_PREP]);
+    cudaEventElapsedTime(&t.max_ms, c->ev[EV_PREP], c->ev[EV_MAX]);
+    cudaEventElapsedTime(&t.score_ms, c->ev[EV_MAX], c->ev[EV_SCORE]);
+    cudaEventElapsedTime(&t.write_ms, c->ev[EV_SCORE], c->ev[EV_WRITE]);
+    if (copies) {
+        cudaEventElapsedTime(&t.h2d_ms, c->ev[EV_H2D0], c->ev[EV_H2D1]);
+        cudaEventElapsedTime(&t.d2h_ms, c->ev[EV_D2H0], c->ev[EV_D2H1]);
+    }
+    t.kernels = c->launches;
+    t.path = 0;
+    cudaGetLastError();
+}
+
+static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
+    TRY(phase0(c, d_req));
+    TRY(exchange_locked(c, 0));
+    TRY(phase1(c));
+    TRY(exchange_locked(c, 1));
+    TRY(phase2(c));
+    TRY(exchange_locked(c, 2));
+    TRY(phase3(c));
+    c->ph_done = 3;
+    c->last_P = c->ph_P;
+    c->last_full = (c->ph_flags & YODA_EVAL_FULL) != 0;
+    return YODA_OK;
+}
+
+extern "C" int yoda_eval_batch(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32 flags, yoda_pod_result *out) {
+    if (!c || (P && (!pods || !out))) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (P == 0) return YODA_OK;
+    TRY(begin_locked(c, P, flags));
+    cudaStream_t st = c->stream;
+    CU(cudaEventRecord(c->ev[EV_H2D0], st));
+    CU(cudaMemcpyAsync(c->d_req, pods, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, st));
+    CU(cudaEventRecord(c->ev[EV_H2D1], st));
+    TRY(run_all_locked(c, c->d_req));
+    CU(cudaEventRecord(c->ev[EV_D2H0], st));
+    CU(cudaMemcpyAsync(out, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(c->ev[EV_D2H1], st));
+    CU(cudaStreamSynchronize(st));
+    collect_timing(c, true);
+    return YODA_OK;
+}
+
+extern "C" int yoda_eval_batch_device(yoda_ctx *c, const void *d_pods, u32 P, u32 flags, void *d_out) {
+    if (!c || (P && !d_pods)) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (P == 0) return YODA_OK;
+    TRY(begin_locked(c, P, flags));
+    TRY(run_all_locked(c, (const yoda_pod_req *)d_pods));
+    if (d_out)
+        CU(cudaMemcpyAsync(d_out, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToDevice, c->stream));
+    return YODA_OK;
+}
+
+extern "C" int yoda_sync(yoda_ctx *c) {
+    if (!c) return fail(YODA_E_ARG, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    CU(cudaStreamSynchronize(c->stream));
+    return YODA_OK;
+}
+
+extern "C" int yoda_last_timing(yoda_ctx *c, yoda_timing *t) {
+    if (!c || !t) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (c->ph_done != 3) return fail(YODA_E_STATE, "no completed evaluation");
+    CU(cudaStreamSynchronize(c->stream));
+    const bool had_copies = c->timing.h2d_ms != 0.f;
+    collect_timing(c, had_copies);
+    *t = c->timing;
+    return YODA_OK;
+}
+
+extern "C" int yoda_fetch_row(yoda_ctx *c, u32 pod, int kind, void *dst, size_t bytes) {
+    if (!c || !dst) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (!c->last_full || pod >= c->last_P)
+        return fail(YODA_E_STATE, "no YODA_EVAL_FULL result holds pod %u (last batch: %u pods, full=%d)", pod, c->last_P,
+                    (int)c->last_full);
+    const void *src;
+    size_t row;
+    switch (kind) {
+        case YODA_ROW_FEASIBLE_BITS: src = c->d_bits + (size_t)pod * (c->stride / 32); row = (c->stride / 32) * 4; break;
+        case YODA_ROW_RAW: src = c->d_raw + (size_t)pod * c->stride; row = c->stride * 8; break;
+        case YODA_ROW_NORM: src = c->d_norm + (size_t)pod * c->stride; row = c->stride; break;
+        default: return fail(YODA_E_ARG, "unknown row kind %d", kind);
+    }
+    if (bytes > row) return fail(YODA_E_RANGE, "row kind %d holds %zu bytes, %zu requested", kind, row, bytes);
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return YODA_OK;
+}
+
+extern "C" int yoda_result_matrices(yoda_ctx *c, void **d_bits, void **d_raw, void **d_norm, uint64_t *stride) {
+    if (!c) return fail(YODA_E_ARG, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!c->last_full) return fail(YODA_E_STATE, "no YODA_EVAL_FULL result");
+    if (d_bits) *d_bits = c->d_bits;
+    if (d_raw) *d_raw = c->d_raw;
+    if (d_norm) *d_norm = c->d_norm;
+    if (stride) *stride = c->stride;
+    return YODA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// phase-split API (host-driven exchange)
+// ------------------------------------------------------------------------------------------
+extern "C" int yoda_phase_begin(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32 flags) {
+    if (!c || !pods || P == 0) return fail(YODA_E_ARG, "null argument or empty batch");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    TRY(begin_locked(c, P, flags));
+    CU(cudaMemcpyAsync(c->d_req, pods, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));  // caller's buffer may be pageable and is not retained
+    return YODA_OK;
+}
+
+extern "C" int yoda_phase_run(yoda_ctx *c, int phase) {
+    if (!c) return fail(YODA_E_ARG, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (c->ph_P == 0 || phase != c->ph_done + 1 || phase > 3)
+        return fail(YODA_E_STATE, "phase %d requested after phase %d", phase, c->ph_done);
+    switch (phase) {
+        case 0: TRY(phase0(c, c->d_req)); break;
+        case 1: TRY(phase1(c)); break;
+        case 2: TRY(phase2(c)); break;
+        case 3: TRY(phase3(c)); break;
+    }
+    c->ph_done = phase;
+    if (phase == 3) {
+        c->last_P = c->ph_P;
+        c->last_full = (c->ph_flags & YODA_EVAL_FULL) != 0;
+    }
+    CU(cudaStreamSynchronize(c->stream));  // exchange buffers are handed to a foreign collective next
+    return YODA_OK;
+}
+
+extern "C" int yoda_phase_exchange(yoda_ctx *c, int phase, yoda_xchg *bufs, int *n_bufs) {
+    if (!c || !bufs || !n_bufs) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (phase > c->ph_done) return fail(YODA_E_STATE, "phase %d has not run", phase);
+    const u64 P = c->ph_P;
+    int k = 0;
+    auto put = [&](void *p, u64 n, int op) {
+        if (k < *n_bufs) bufs[k] = yoda_xchg{p, n, op, 0};
+        ++k;
+    };
+    if (phase == 0) {
+        put(c->d_max6, P * 6, YODA_XCHG_MAX);
+        put(c->d_count, P, YODA_XCHG_SUM);
+    } else if (phase == 1) {
+        put(c->d_hilo, P * 2, YODA_XCHG_MAX);
+    } else if (phase == 2) {
+        put(c->d_ckey, P, YODA_XCHG_MAX);
+    }
+    if (k > *n_bufs) return fail(YODA_E_RANGE, "need %d exchange descriptors", k);
+    *n_bufs = k;
+    return YODA_OK;
+}
+
+extern "C" int yoda_phase_finish(yoda_ctx *c, yoda_pod_result *out) {
+    if (!c || !out) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (c->ph_done != 3) return fail(YODA_E_STATE, "phase 3 has not run");
+    CU(cudaMemcpyAsync(out, c->d_res, (size_t)c->ph_P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    collect_timing(c, false);
+    return YODA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// NormalizeScore on a caller-supplied list
+// ------------------------------------------------------------------------------------------
+extern "C" int yoda_normalize_scores(yoda_ctx *c, int64_t *scores, u32 n) {
+    if (!c || !scores) return fail(YODA_E_ARG, "null argument");
+    if (n == 0) return fail(YODA_E_ARG, "empty score list (the reference indexes scores[0], scheduler.go:135)");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (n > c->list_cap) {
+        CU(cudaStreamSynchronize(c->stream));
+        dev_free(c->d_list);
+        c->list_cap = 0;
+        TRY(dev_alloc(&c->d_list, round_up(n, 4096)));
+        c->list_cap = round_up(n, 4096);
+    }
+    cudaStream_t st = c->stream;
+    const i64 init[2] = {(i64)scores[0], 0};
+    CU(cudaMemcpyAsync(c->d_list, scores, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(c->d_lohi, init, sizeof init, cudaMemcpyHostToDevice, st));
+    const u32 blocks = std::min<u32>((n + 255) / 256, 1184);
+    k_norm_list_reduce<<<blocks, 256, 0, st>>>(c->d_list, n, c->d_lohi);
+    CU(cudaGetLastError());
+    k_norm_list_apply<<<blocks, 256, 0, st>>>(c->d_list, n, c->d_lohi);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(scores, c->d_list, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return YODA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// label parsing (host): strconv.Atoi with error -> 0, then the uint/uint64 conversion
+// ------------------------------------------------------------------------------------------
+extern "C" uint64_t yoda_parse_label(const char *s, size_t len) {
+    if (!s || len == 0) return 0;
+    size_t i = 0;
+    bool neg = false;
+    if (s[0] == '+' || s[0] == '-') {
+        neg = s[0] == '-';
+        i = 1;
+    }
+    if (i == len) return 0;
+    // accumulate in 128 bits so that overflow detection needs no pre-division
+    unsigned __int128 acc = 0;
+    const unsigned __int128 lim = neg ? ((unsigned __int128)1 << 63) : (((unsigned __int128)1 << 63) - 1);
+    for (; i < len; ++i) {
+        const unsigned char ch = (unsigned char)s[i];
+        if (ch < '0' || ch > '9') return 0;  // syntax error
+        acc = acc * 10 + (ch - '0');
+        if (acc > lim) return 0;  // range error
+    }
+    const uint64_t mag = (uint64_t)acc;
+    return neg ? (uint64_t)(0 - mag) : mag;
+}
+
+extern "C" int64_t yoda_uint64_to_int64(uint64_t v) { return (v >> 63) ? 0 : (int64_t)v; }
+
+// ------------------------------------------------------------------------------------------
+// NCCL communicator
+// ------------------------------------------------------------------------------------------
+extern "C" int yoda_comm_unique_id(void *id128) {
+    if (!id128) return fail(YODA_E_ARG, "null argument");
+    TRY(nccl_load());
+    static_assert(sizeof(ncclUniqueId) == YODA_NCCL_ID_BYTES, "ncclUniqueId size");
+    ncclUniqueId id;
+    NC(g_nccl.GetUniqueId(&id));
+    memcpy(id128, &id, sizeof id);
+    return YODA_OK;
+}
+
+extern "C" int yoda_comm_init(yoda_ctx *c, const void *id128, u32 rank, u32 n_ranks) {
+    if (!c || !id128) return fail(YODA_E_ARG, "null argument");
+    if (n_ranks != c->cfg.shard_count || rank != c->cfg.shard_rank)
+        return fail(YODA_E_ARG, "communicator rank %u/%u does not match the context's shard %u/%u", rank, n_ranks,
+                    c->cfg.shard_rank, c->cfg.shard_count);
+    TRY(nccl_load());
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    ncclUniqueId id;
+    memcpy(&id, id128, sizeof id);
+    NC(g_nccl.CommInitRank(&c->comm, (int)n_ranks, id, (int)rank));
+    return YODA_OK;
+}
