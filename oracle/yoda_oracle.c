@@ -408,7 +408,7 @@ int ora_cluster_set_node_pods(ora_cluster *c, uint32_t idx, uint32_t n_pods, con
 }
 
 /* Bulk fill from flat arrays ([n][8] card planes, healthy bitmask).  Running pods are given
- * as a CSR list of scv/memory values and rendered to decimal label strings. */
+ * as a CSR list of StrToUint64(scv/memory) values and rendered back to decimal label strings. */
 int ora_cluster_fill(ora_cluster *c, const uint8_t *has_scv, const uint64_t *card_number, const uint8_t *n_cards,
                      const uint8_t *healthy_mask, const uint64_t *free_memory, const uint64_t *total_memory,
                      const uint64_t *clock, const uint64_t *core, const uint64_t *bandwidth, const uint64_t *power,
@@ -431,7 +431,8 @@ int ora_cluster_fill(ora_cluster *c, const uint8_t *has_scv, const uint64_t *car
                 nkv[i] = 1;
                 keys[i] = "scv/memory";
                 vals[i] = (char *)malloc(24);
-                snprintf(vals[i], 24, "%llu", (unsigned long long)pod_mem[pod_off[n] + i]);
+                /* signed rendering, so that values >= 2^63 (labels such as "-5") survive Atoi */
+                snprintf(vals[i], 24, "%lld", (long long)pod_mem[pod_off[n] + i]);
             }
             ora_cluster_set_node_pods(c, n, np, nkv, keys, (const char *const *)vals);
             for (uint32_t i = 0; i < np; ++i) free(vals[i]);

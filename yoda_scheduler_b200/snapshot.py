@@ -117,7 +117,7 @@ class Snapshot:
                       "free": int(self.free_memory[i, g]), "total": int(self.total_memory[i, g]), "clock": int(self.clock[i, g]),
                       "core": int(self.core[i, g]), "bandwidth": int(self.bandwidth[i, g]), "power": int(self.power[i, g])}
                      for g in range(int(self.n_cards[i]))]
-            pods = [{"scv/memory": str(int(m))} for m in self.pod_mem[self.pod_off[i]:self.pod_off[i + 1]]]
+            pods = [{"scv/memory": str(int(m) - (1 << 64) if int(m) >> 63 else int(m))} for m in self.pod_mem[self.pod_off[i]:self.pod_off[i + 1]]]
             out.append({"name": self.names[i] if self.names else f"node-{i}", "has_scv": bool(self.has_scv[i]),
                         "card_number": int(self.card_number[i]), "cards": cards, "free_sum": int(self.free_memory_sum[i]),
                         "total_sum": int(self.total_memory_sum[i]), "pods": pods})
