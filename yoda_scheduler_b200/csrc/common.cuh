@@ -34,8 +34,7 @@ struct DevSnap {
     u64 *stat;          // [cap] allocate score + actual score (algorithm.go:70-87), derived
     u32 *meta;          // [cap]
     // narrow planes, derived (valid when the snapshot is narrow-eligible)
-    u32 *free32;        // [cap][G]
-    u32 *clock32;       // [cap][G]
+    u32 *n32[NFIELD];   // [cap][G] uint32 copies of the card planes
     u32 *cardnum32;     // [cap]
     u32 *stat32;        // [cap]
     u32 n_nodes;        // committed node count (highest index + 1)

@@ -76,8 +76,8 @@ __global__ void k_prepare(DevSnap s, u32 *wide_flag) {
 #pragma unroll
         for (int f = 0; f < NFIELD; ++f) any |= (s.f[f][o] >= NARROW_FIELD_LIMIT) ? 1ull : 0ull;
         wide |= (any != 0) && (meta & META_HAS_SCV);
-        s.free32[o] = (u32)s.f[F_FREE][o];
-        s.clock32[o] = (u32)s.f[F_CLOCK][o];
+#pragma unroll
+        for (int f = 0; f < NFIELD; ++f) s.n32[f][o] = (u32)s.f[f][o];
     }
     if (wide) atomicOr(wide_flag, 1u);
 }
@@ -187,17 +187,18 @@ __device__ __forceinline__ void direct_load_tile(DirectTile &sm, const DevSnap &
     }
 }
 
-// MODE 0: collection.CollectMaxValues + feasible count.  MODE 1: Score reduce (lowest/highest).
+// MODE 0: collection.CollectMaxValues.  MODE 1: Score reduce (lowest/highest).
 template <int MODE>
 __global__ void __launch_bounds__(DPT) k_direct_pods(DevSnap s, const PodC *__restrict__ pods, u32 P, u32 nodes_per_cta,
-                                                     u64 *max6, u64 *count, u64 *hilo) {
+                                                     u64 *max6, u64 *hilo) {
     __shared__ DirectTile sm;
     const u32 p = blockIdx.x * DPT + threadIdx.x;
     const bool active = p < P;
     PodC pod;
     if (active) pod = pods[p];
     u64 mx[6] = {1, 1, 1, 1, 1, 1};
-    u64 cnt = 0, hi = 0, nlo = 0;
+    u64 hi = 0, nlo = 0;
+    bool any = false;
     if (MODE == 1 && active) {
 #pragma unroll
         for (int i = 0; i < 6; ++i) mx[i] = max6[(size_t)p * 6 + i];
@@ -215,7 +216,7 @@ __global__ void __launch_bounds__(DPT) k_direct_pods(DevSnap s, const PodC *__re
             const bool fit = direct_fit(pod, sm.meta[i], sm.cardnum[i], &sm.f[F_FREE][i * G], &sm.f[F_CLOCK][i * G], qual);
             if (!fit) continue;
             if (MODE == 0) {
-                cnt++;
+                any = true;
                 for (int g = 0; g < G; ++g) {
                     if ((qual >> g) & 1u) {  // collection.go:59-78
                         mx[0] = max(mx[0], sm.f[F_BW][i * G + g]);
@@ -240,8 +241,7 @@ __global__ void __launch_bounds__(DPT) k_direct_pods(DevSnap s, const PodC *__re
     }
     if (!active) return;
     if (MODE == 0) {
-        if (cnt) {
-            atomicAdd(&count[p], cnt);
+        if (any) {
 #pragma unroll
             for (int i = 0; i < 6; ++i)
                 if (mx[i] > 1) atomicMax(&max6[(size_t)p * 6 + i], mx[i]);
@@ -255,8 +255,8 @@ __global__ void __launch_bounds__(DPT) k_direct_pods(DevSnap s, const PodC *__re
 }
 
 // lowest/highest as NormalizeScore uses them (scheduler.go:134-149), from the reduced partials
-__device__ __forceinline__ void dev_lo_hi(const u64 *hilo, u32 p, u64 cnt, i64 &lo, i64 &hi) {
-    if (cnt == 0) {
+__device__ __forceinline__ void dev_lo_hi(const u64 *hilo, u32 p, i64 &lo, i64 &hi) {
+    if (hilo[2 * (size_t)p + 1] == 0) {  // identity: no feasible node on any shard
         lo = 0;
         hi = 0;
         return;
@@ -274,7 +274,7 @@ __device__ __forceinline__ void dev_lo_hi(const u64 *hilo, u32 p, u64 cnt, i64 &
 #define DCT 128  // nodes (threads) per CTA
 template <bool WRITE>
 __global__ void __launch_bounds__(DCT) k_direct_out(DevSnap s, const PodC *__restrict__ pods, u32 P, u32 pods_per_cta,
-                                                    const u64 *__restrict__ max6, const u64 *__restrict__ count,
+                                                    const u64 *__restrict__ max6, u64 *count,
                                                     const u64 *__restrict__ hilo, u64 *ckey, i64 *raw_out, u8 *norm_out,
                                                     u32 *bits_out, u64 stride) {
     const u32 n = blockIdx.x * DCT + threadIdx.x;
@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(DCT) k_direct_out(DevSnap s, const PodC *__res
 #pragma unroll
         for (int i = 0; i < 6; ++i) mx[i] = max6[(size_t)p * 6 + i];
         i64 lo, hi;
-        dev_lo_hi(hilo, p, count[p], lo, hi);
+        dev_lo_hi(hilo, p, lo, hi);
         u32 qual;
         const bool fit = direct_fit(pod, meta, cardnum, fr, ck, qual);
         u64 basic = 0;
@@ -320,6 +320,7 @@ __global__ void __launch_bounds__(DCT) k_direct_out(DevSnap s, const PodC *__res
         const u32 fitmask = __ballot_sync(0xFFFFFFFFu, fit);
         const u32 topmask = __ballot_sync(0xFFFFFFFFu, fit && raw == hi);
         if (topmask && (threadIdx.x & 31) == (u32)(__ffs(topmask) - 1)) atomicMax(&ckey[p], ckey_of(s.node_base + n));
+        if (fitmask && (threadIdx.x & 31) == 0) atomicAdd(&count[p], (u64)__popc(fitmask));
         if (WRITE) {
             if (live) {
                 raw_out[(size_t)p * stride + n] = raw;
@@ -344,7 +345,7 @@ __global__ void k_finalize(const u64 *__restrict__ max6, const u64 *__restrict__
     r.max_power = max6[(size_t)p * 6 + 4];
     r.max_total_memory = max6[(size_t)p * 6 + 5];
     i64 lo, hi;
-    dev_lo_hi(hilo, p, count[p], lo, hi);
+    dev_lo_hi(hilo, p, lo, hi);
     r.lowest = lo;
     r.highest = hi;
     r.feasible = (u32)count[p];

@@ -1,0 +1,627 @@
+// fast_kernels.cuh -- the narrow (uint32) fast path.
+//
+// Applies when k_prepare found every card field and CardNumber < 2^32-1 and every static score
+// < 2^24 (any real cluster).  It produces bit-identical results to the direct kernels with far
+// fewer integer operations per (pod, node) pair:
+//
+//  1. pods are hashed into requirement groups (has-clock, clock, number, has-memory) and sorted by
+//     (group, memory);
+//  2. collection.CollectMaxValues becomes a 1-D dominance problem per group: a card counts for a
+//     pod iff memory <= e(card) with e = min(FreeMemory, k-th largest healthy FreeMemory of its
+//     node), so each card binary-searches the group's sorted memory values once and a suffix-max
+//     scan over the pods finishes the six maxima -- O((cards + pods) log pods) per group instead
+//     of O(pods x cards);
+//  3. pods with the same six maxima form a class; per class a table of per-card scores
+//     (algorithm.go:57-68, six real divisions) is built once per batch;
+//  4. the two hot kernels (score reduce, output pass) run lane = node with the node's eight
+//     FreeMemory values and eight class card scores in registers and loop over the sorted pods:
+//     one compare + one predicated add per card, the healthy-card count for Filter riding in
+//     bits 24..27 of the same sum.
+#pragma once
+#include "common.cuh"
+
+// sorted pod record (32 B), broadcast to every lane of the hot kernels
+struct PodS {
+    u32 m, c, num;  // memory / clock / number, clamped to 2^32-1
+    u32 req;        // bits 0-7 reqM (number if scv/memory present else 0), bits 8-15 reqC, bits 16-18 label flags
+    u32 cls;        // class id (index of the card-score table)
+    u32 orig;       // index in the caller's batch
+    u32 gid;        // requirement group
+    u32 pad;
+};
+// rescale constants of one pod for the output pass: norm = ((raw - lo) * 100 * M) >> 57
+struct PodNrm {
+    u32 lo, hi, mhi, mlo;
+};
+struct GroupDesc {
+    u32 flags, c, num, seg_start, seg_end, pad0, pad1, pad2;
+};
+
+#define CS_HEALTH_SHIFT 24
+#define CS_SCORE_MASK 0xFFFFFFu
+#define CS_LIMIT (1u << 21)  // admissible card scores must stay below this (8 cards -> sum < 2^24)
+
+#define FAST_GID_BITS 12
+#define FAST_GROUP_CAP (1u << FAST_GID_BITS)  // more requirement groups than this -> direct path
+#define FAST_ERR_HASH 1u        // 64-bit hash collision between two different tuples
+#define FAST_ERR_WIDE_CLASS 2u  // a class table entry does not fit the packed format
+#define FAST_ERR_CAP 4u         // group/class capacity exceeded
+
+// counters shared between the grouping kernels and the host
+struct FastCtl {
+    u32 n_groups, n_classes, p0 /* first sorted position with scv/clock present */, err;
+};
+
+__device__ __forceinline__ u32 clamp32(u64 v) { return v > 0xFFFFFFFFull ? 0xFFFFFFFFu : (u32)v; }
+__device__ __forceinline__ u64 mix64(u64 z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// ------------------------------------------------------------------------------------------
+// open-addressing set of 64-bit keys; empty = all ones.  Insert only publishes the key; dense ids
+// are handed out by k_hash_compact, so no thread ever waits on another.
+// ------------------------------------------------------------------------------------------
+#define HASH_EMPTY 0xFFFFFFFFFFFFFFFFull
+__device__ __forceinline__ u32 hash_insert(u64 *keys, u32 mask, u64 key) {
+    u32 slot = (u32)mix64(key) & mask;
+    for (;;) {
+        u64 cur = keys[slot];
+        if (cur == key) return slot;
+        if (cur == HASH_EMPTY) {
+            cur = atomicCAS(&keys[slot], HASH_EMPTY, key);
+            if (cur == HASH_EMPTY || cur == key) return slot;
+        }
+        slot = (slot + 1) & mask;
+    }
+}
+__global__ void k_hash_clear(u64 *keys, u32 *rep, u32 n) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        keys[i] = HASH_EMPTY;
+        rep[i] = 0xFFFFFFFFu;
+    }
+}
+// occupied slot -> dense id (order arbitrary; results never depend on it)
+__global__ void k_hash_compact(const u64 *keys, u32 *ids, u32 n, u32 *counter) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && keys[i] != HASH_EMPTY) ids[i] = atomicAdd(counter, 1u);
+}
+
+// ------------------------------------------------------------------------------------------
+// step 1: requirement groups
+// ------------------------------------------------------------------------------------------
+// group key: everything Filter/CollectMaxValues read from the pod except the memory value
+__device__ __forceinline__ u64 group_key(const PodC &p, u32 &num32, u32 &c32, u32 &gflags) {
+    num32 = clamp32(p.num);
+    c32 = (p.flags & YODA_POD_HAS_CLOCK) ? clamp32(p.clk) : 0u;
+    gflags = p.flags & (YODA_POD_HAS_MEMORY | YODA_POD_HAS_CLOCK);
+    if (gflags) {
+        // with a per-card count requirement, every number > 8 is equally infeasible (<= 8 cards per node)
+        if (num32 > G) { num32 = G + 1; c32 = 0; }
+        return (1ull << 63) | ((u64)(gflags & YODA_POD_HAS_MEMORY ? 1 : 0) << 62) | ((u64)(gflags & YODA_POD_HAS_CLOCK ? 1 : 0) << 61) |
+               ((u64)num32 << 32) | c32;
+    }
+    return (u64)num32;
+}
+
+__global__ void k_group_insert(const PodC *__restrict__ pods, u32 P, u64 *gkeys, u32 gmask, u32 *slot_of_pod) {
+    u32 p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    u32 n32, c32, gf;
+    const u64 key = group_key(pods[p], n32, c32, gf);
+    slot_of_pod[p] = hash_insert(gkeys, gmask, key);
+}
+
+// pod -> gid, sort key (has-clock | gid | memory), group descriptor
+__global__ void k_group_assign(const PodC *__restrict__ pods, u32 P, const u32 *__restrict__ slot_of_pod,
+                               const u32 *__restrict__ gids, GroupDesc *gdesc, u32 gcap, u64 *sort_keys, u32 *sort_vals,
+                               u32 *pod_gid, FastCtl *ctl) {
+    u32 p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const PodC pod = pods[p];
+    u32 n32, c32, gf;
+    group_key(pod, n32, c32, gf);
+    const u32 gid = gids[slot_of_pod[p]];
+    pod_gid[p] = gid;
+    const u32 m32 = clamp32(pod.mem);
+    sort_keys[p] = ((u64)(gf & YODA_POD_HAS_CLOCK ? 1 : 0) << (32 + FAST_GID_BITS)) | ((u64)(gid & (FAST_GROUP_CAP - 1)) << 32) | m32;
+    sort_vals[p] = p;
+    if (gid < gcap) {
+        // every pod of the group writes the same values
+        gdesc[gid].flags = gf;
+        gdesc[gid].c = c32;
+        gdesc[gid].num = n32;
+    } else {
+        atomicOr(&ctl->err, FAST_ERR_CAP);
+    }
+}
+
+// sorted pod records + group segment bounds + first clock position
+__global__ void k_build_sorted(const PodC *__restrict__ pods, u32 P, const u64 *__restrict__ keys_sorted,
+                               const u32 *__restrict__ vals_sorted, GroupDesc *gdesc, u32 gcap, PodS *out, u32 *m_sorted,
+                               FastCtl *ctl) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const u64 key = keys_sorted[i];
+    const u32 orig = vals_sorted[i];
+    const PodC pod = pods[orig];
+    u32 n32, c32, gf;
+    group_key(pod, n32, c32, gf);
+    const u32 gid = (u32)(key >> 32) & (FAST_GROUP_CAP - 1);
+    PodS s;
+    s.m = (u32)key;
+    s.c = (pod.flags & YODA_POD_HAS_CLOCK) ? clamp32(pod.clk) : 0u;
+    s.num = clamp32(pod.num);
+    const u32 req = min(s.num, 255u);
+    s.req = ((pod.flags & YODA_POD_HAS_MEMORY) ? req : 0u) | (((pod.flags & YODA_POD_HAS_CLOCK) ? req : 0u) << 8) | (pod.flags << 16);
+    s.cls = 0;
+    s.orig = orig;
+    s.gid = gid;
+    s.pad = 0;
+    out[i] = s;
+    m_sorted[i] = s.m;
+    const bool head = (i == 0) || ((u32)(keys_sorted[i - 1] >> 32) != (u32)(key >> 32));
+    const bool tail = (i == P - 1) || ((u32)(keys_sorted[i + 1] >> 32) != (u32)(key >> 32));
+    if (gid < gcap) {
+        if (head) gdesc[gid].seg_start = i;
+        if (tail) gdesc[gid].seg_end = i + 1;
+    }
+    if (head && ((key >> (32 + FAST_GID_BITS)) & 1ull)) atomicMin(&ctl->p0, i);
+}
+
+// ------------------------------------------------------------------------------------------
+// step 2: CollectMaxValues as dominance queries.  thread = (node, group).
+// step[f][i] (sorted pod position i) receives the maxima of the cards whose LAST admissible pod is i;
+// k_max_scan turns that into the maxima of all cards admissible for pod i.
+// ------------------------------------------------------------------------------------------
+#define MAXT 128
+__global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupDesc *__restrict__ gdesc, u32 n_groups,
+                                                         const u32 *__restrict__ m_sorted, u32 *step, u32 P) {
+    const u32 gid = blockIdx.y;
+    const u32 n = blockIdx.x * MAXT + threadIdx.x;
+    if (gid >= n_groups || n >= s.n_nodes) return;
+    const GroupDesc gd = gdesc[gid];
+    const u32 meta = s.meta[n];
+    if (!(meta & META_HAS_SCV)) return;
+    if (gd.num > s.cardnum32[n]) return;  // filter.go:13,15
+    const u32 nc = meta_ncards(meta), hm = meta_healthy(meta);
+    u32 fr[G], ck[G];
+    const uint4 *pf = reinterpret_cast<const uint4 *>(s.n32[F_FREE] + (size_t)n * G);
+    const uint4 *pc = reinterpret_cast<const uint4 *>(s.n32[F_CLOCK] + (size_t)n * G);
+    uint4 a = pf[0], b = pf[1];
+    fr[0] = a.x; fr[1] = a.y; fr[2] = a.z; fr[3] = a.w; fr[4] = b.x; fr[5] = b.y; fr[6] = b.z; fr[7] = b.w;
+    a = pc[0]; b = pc[1];
+    ck[0] = a.x; ck[1] = a.y; ck[2] = a.z; ck[3] = a.w; ck[4] = b.x; ck[5] = b.y; ck[6] = b.z; ck[7] = b.w;
+    if (gd.flags & YODA_POD_HAS_CLOCK) {  // filter.go:35-50
+        u32 cnt = 0;
+#pragma unroll
+        for (int g = 0; g < G; ++g) cnt += ((hm >> g) & 1u) & (u32)(ck[g] == gd.c);
+        if (cnt < gd.num) return;
+    }
+    // node admits memory values m <= T: T = num-th largest FreeMemory among healthy cards (filter.go:18-33)
+    u32 T = 0xFFFFFFFFu;
+    if ((gd.flags & YODA_POD_HAS_MEMORY) && gd.num >= 1) {
+        if ((u32)__popc(hm) < gd.num) return;
+        T = 0;
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            if ((hm >> g) & 1u) {
+                u32 rank = 0;
+#pragma unroll
+                for (int h = 0; h < G; ++h)
+                    if (((hm >> h) & 1u) && (fr[h] > fr[g] || (fr[h] == fr[g] && h < g))) rank++;
+                if (rank == gd.num - 1) T = fr[g];
+            }
+        }
+    }
+    const u32 *ms = m_sorted + gd.seg_start;
+    const u32 len = gd.seg_end - gd.seg_start;
+    for (int g = 0; g < (int)nc; ++g) {
+        if (ck[g] < gd.c) continue;  // collection.go:46 (clock >= c; c == 0 without the label)
+        const u32 e = min(fr[g], T);
+        // j = number of pods of the group with memory <= e
+        u32 lo = 0, hi = len;
+        while (lo < hi) {
+            const u32 mid = (lo + hi) >> 1;
+            if (ms[mid] <= e) lo = mid + 1; else hi = mid;
+        }
+        if (lo == 0) continue;
+        const u32 pos = gd.seg_start + lo - 1;
+        const size_t o = (size_t)n * G + g;
+        // collection.go:59-78; order of the step planes = collection.MaxValue (bw, clock, core, free, power, total)
+        const u32 v[6] = {s.n32[F_BW][o], ck[g], s.n32[F_CORE][o], fr[g], s.n32[F_POWER][o], s.n32[F_TOTAL][o]};
+#pragma unroll
+        for (int f = 0; f < 6; ++f)
+            if (v[f] > step[(size_t)f * P + pos]) atomicMax(&step[(size_t)f * P + pos], v[f]);
+    }
+}
+
+// one CTA per group: suffix maximum over the group's pod segment, result max(1, .) into max6[orig]
+#define SCANT 256
+__global__ void __launch_bounds__(SCANT) k_max_scan(const GroupDesc *__restrict__ gdesc, u32 n_groups, const u32 *__restrict__ step,
+                                                    const PodS *__restrict__ pods, u64 *max6, u32 P) {
+    const u32 gid = blockIdx.x;
+    if (gid >= n_groups) return;
+    const GroupDesc gd = gdesc[gid];
+    __shared__ u32 warp_max[6][SCANT / 32];
+    __shared__ u32 carry_s[6];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x < 6) carry_s[threadIdx.x] = 0;
+    __syncthreads();
+    // walk the segment backwards in tiles of SCANT; thread t handles position end-1-t of the tile
+    for (u32 top = gd.seg_end; top > gd.seg_start;) {
+        const u32 cnt = min(SCANT, top - gd.seg_start);
+        const bool live = threadIdx.x < cnt;
+        const u32 pos = live ? top - 1 - threadIdx.x : 0;
+        u32 v[6];
+#pragma unroll
+        for (int f = 0; f < 6; ++f) v[f] = live ? step[(size_t)f * P + pos] : 0u;
+        // inclusive prefix max over threadIdx (= suffix max over positions)
+#pragma unroll
+        for (int f = 0; f < 6; ++f) {
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const u32 t = __shfl_up_sync(0xFFFFFFFFu, v[f], o);
+                if (lane >= (u32)o) v[f] = max(v[f], t);
+            }
+            if (lane == 31) warp_max[f][warp] = v[f];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int f = 0; f < 6; ++f) {
+            u32 pre = carry_s[f];
+            for (u32 w = 0; w < warp; ++w) pre = max(pre, warp_max[f][w]);
+            v[f] = max(v[f], pre);
+        }
+        if (live) {
+            const u32 orig = pods[pos].orig;
+#pragma unroll
+            for (int f = 0; f < 6; ++f) max6[(size_t)orig * 6 + f] = (u64)max(v[f], 1u);  // collection.go:31-38
+        }
+        __syncthreads();
+        if (threadIdx.x == SCANT - 1) {
+#pragma unroll
+            for (int f = 0; f < 6; ++f) carry_s[f] = v[f];
+        }
+        __syncthreads();
+        top -= cnt;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// step 3: classes = distinct (reduced) maxima tuples
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ u64 class_hash(const u64 *mx) {
+    u64 h = 0x9E3779B97F4A7C15ull;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) h = mix64(h ^ mx[i]) + 0x9E3779B97F4A7C15ull * (i + 1);
+    return h & 0x7FFFFFFFFFFFFFFFull;  // never HASH_EMPTY
+}
+__global__ void k_class_insert(const PodS *__restrict__ pods, u32 P, const u64 *__restrict__ max6, u64 *ckeys, u32 cmask, u32 *rep,
+                               u32 *slot_of_pod) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const u32 orig = pods[i].orig;
+    const u32 slot = hash_insert(ckeys, cmask, class_hash(max6 + (size_t)orig * 6));
+    slot_of_pod[i] = slot;
+    if (rep[slot] > orig) atomicMin(&rep[slot], orig);  // a deterministic representative pod
+}
+// pod -> class id; verify the tuple against the representative's (hash collisions -> error flag);
+// the representative records the class maxima
+__global__ void k_class_assign(PodS *pods, u32 P, const u64 *__restrict__ max6, const u32 *__restrict__ rep,
+                               const u32 *__restrict__ cids, const u32 *__restrict__ slot_of_pod, u32 *cls_max, u32 ccap, FastCtl *ctl) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const u32 slot = slot_of_pod[i];
+    const u32 cid = cids[slot], r = rep[slot], orig = pods[i].orig;
+    bool same = true, narrow = true;
+#pragma unroll
+    for (int f = 0; f < 6; ++f) {
+        same &= max6[(size_t)orig * 6 + f] == max6[(size_t)r * 6 + f];
+        narrow &= max6[(size_t)orig * 6 + f] <= 0xFFFFFFFFull;  // another shard may be wide
+    }
+    if (!same) atomicOr(&ctl->err, FAST_ERR_HASH);
+    if (!narrow) atomicOr(&ctl->err, FAST_ERR_WIDE_CLASS);
+    pods[i].cls = cid;
+    if (cid >= ccap) {
+        atomicOr(&ctl->err, FAST_ERR_CAP);
+    } else if (orig == r) {
+#pragma unroll
+        for (int f = 0; f < 6; ++f) cls_max[(size_t)cid * 6 + f] = (u32)max6[(size_t)r * 6 + f];
+    }
+}
+
+// exact floor(x * 100 / d) for x, d < 2^32, d >= 1
+__device__ __forceinline__ u32 div100(u32 x, u32 d, bool &big) {
+    const u64 a = (u64)x * 100ull;
+    const u64 q = (a >> 32) ? a / (u64)d : (u64)((u32)a / d);
+    big |= q >= CS_LIMIT;
+    return (u32)q;
+}
+
+// Per class, per card: CalculateCardScore (algorithm.go:57-68) packed with the card's health bit.
+// A card whose fields exceed the class maxima can never be scored by a pod of that class (it would
+// have raised the maxima), so its score slot is 0; its health bit stays (Filter still counts it).
+#define CLST 128
+__global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__restrict__ cls_max, u32 n_classes, u32 *tables,
+                                                       FastCtl *ctl) {
+    const u32 cid = blockIdx.y;
+    const u32 n = blockIdx.x * CLST + threadIdx.x;
+    if (cid >= n_classes || n >= s.n_nodes) return;
+    const u32 mbw = cls_max[cid * 6 + 0], mck = cls_max[cid * 6 + 1], mco = cls_max[cid * 6 + 2], mfr = cls_max[cid * 6 + 3],
+              mpw = cls_max[cid * 6 + 4], mto = cls_max[cid * 6 + 5];
+    const u32 hm = meta_healthy(s.meta[n]);
+    u32 out[G];
+    bool big = false;
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const size_t o = (size_t)n * G + g;
+        const u32 bw = s.n32[F_BW][o], ck = s.n32[F_CLOCK][o], co = s.n32[F_CORE][o], pw = s.n32[F_POWER][o], fr = s.n32[F_FREE][o],
+                  to = s.n32[F_TOTAL][o];
+        u32 cs = 0;
+        if (bw <= mbw && ck <= mck && co <= mco && pw <= mpw && fr <= mfr && to <= mto) {
+            bool b = false;
+            cs = div100(bw, mbw, b) + div100(ck, mbw, b) + div100(co, mco, b) + div100(pw, mpw, b) + div100(fr, mfr, b) * 2u + div100(to, mto, b);
+            b |= cs >= CS_LIMIT;
+            big |= b;
+            cs &= CS_SCORE_MASK;
+        }
+        out[g] = cs | (((hm >> g) & 1u) << CS_HEALTH_SHIFT);
+    }
+    uint4 *dst = reinterpret_cast<uint4 *>(tables + ((size_t)cid * s.cap + n) * G);
+    dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
+    dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
+    if (big) atomicOr(&ctl->err, FAST_ERR_WIDE_CLASS);
+}
+
+// ------------------------------------------------------------------------------------------
+// step 4: the hot kernels.  lane = node (NPL nodes per lane, interleaved by 32), loop over pods.
+// ------------------------------------------------------------------------------------------
+#define HOT_THREADS 256
+#define HOT_WARPS (HOT_THREADS / 32)
+#define HOT_CHUNK 128  // pods per CTA
+
+template <int NPL, bool CLK>
+struct NodeRegs {
+    u32 fr[NPL][G];
+    u32 cs[NPL][G];
+    u32 ck[CLK ? NPL : 1][G];
+    u32 cardnum[NPL];
+    u32 stat[NPL];
+    bool ok[NPL];
+};
+
+__device__ __forceinline__ void load8(const u32 *p, u32 *dst) {
+    const uint4 a = reinterpret_cast<const uint4 *>(p)[0], b = reinterpret_cast<const uint4 *>(p)[1];
+    dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; dst[3] = a.w; dst[4] = b.x; dst[5] = b.y; dst[6] = b.z; dst[7] = b.w;
+}
+
+template <int NPL, bool CLK>
+__device__ __forceinline__ void hot_load_nodes(NodeRegs<NPL, CLK> &r, const DevSnap &s, u32 base, u32 lane) {
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) {
+        const u32 n = base + j * 32 + lane;
+        const bool in = n < s.n_nodes;
+        const u32 nn = in ? n : 0;
+        load8(s.n32[F_FREE] + (size_t)nn * G, r.fr[j]);
+        if (CLK) load8(s.n32[F_CLOCK] + (size_t)nn * G, r.ck[j]);
+        r.cardnum[j] = s.cardnum32[nn];
+        r.stat[j] = in ? s.stat32[nn] : 0u;
+        r.ok[j] = in && (s.meta[nn] & META_HAS_SCV);
+    }
+}
+template <int NPL, bool CLK>
+__device__ __forceinline__ void hot_load_class(NodeRegs<NPL, CLK> &r, const DevSnap &s, const u32 *tables, u32 cls, u32 base, u32 lane) {
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) {
+        const u32 n = base + j * 32 + lane;
+        const u32 nn = n < s.n_nodes ? n : 0;
+        load8(tables + ((size_t)cls * s.cap + nn) * G, r.cs[j]);
+    }
+}
+
+// Filter verdict and Score of (pod, node j): `fit`, raw = basic (if fit) + static part, and
+// `bound` = the smallest FreeMemory of the node that is >= m.  For any m' in [m, bound] the set of
+// cards with FreeMemory >= m' is the same, hence so are fit and raw (same group and class).
+template <int NPL, bool CLK>
+__device__ __forceinline__ u32 hot_eval(const NodeRegs<NPL, CLK> &r, int j, u32 m, u32 c, u32 num, u32 reqM, u32 reqC, bool &fit,
+                                        u32 &bound) {
+    u32 acc = 0, cntc = 0, b = 0xFFFFFFFFu;
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const bool q = r.fr[j][g] >= m;  // filter.go:53 / collection.go:46 / algorithm.go:48
+        b = q ? min(b, r.fr[j][g]) : b;
+        if (CLK) {
+            cntc += (r.ck[j][g] == c) ? (r.cs[j][g] >> CS_HEALTH_SHIFT) : 0u;  // filter.go:57
+            // Filter counts healthy cards on memory alone; the score sum also needs clock >= c.
+            // Keep the health bit on the memory test and the score bits on both.
+            const u32 add = (r.ck[j][g] >= c) ? r.cs[j][g] : (r.cs[j][g] & ~CS_SCORE_MASK);
+            acc += q ? add : 0u;
+        } else {
+            acc += q ? r.cs[j][g] : 0u;
+        }
+    }
+    bound = b;
+    const u32 cnt = acc >> CS_HEALTH_SHIFT;
+    const u32 basic = acc & CS_SCORE_MASK;
+    fit = r.ok[j] && (num <= r.cardnum[j]) && (cnt >= reqM);
+    if (CLK) fit = fit && (cntc >= reqC);
+    return r.stat[j] + (fit ? basic : 0u);  // algorithm.go:38 (no uint64 wrap in the narrow range)
+}
+
+// The pods arrive sorted by (group, memory).  Along that order the verdict and score of a node
+// change only when the memory value crosses one of the node's FreeMemory values, so each lane
+// keeps its last result and the bound up to which it stays valid; a 32-node slot is re-evaluated
+// only when one of its lanes crossed its bound (or the group/class changed).
+
+// score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145)
+template <int NPL, bool CLK>
+__global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
+                                                            const u32 *__restrict__ tables, u64 *hilo) {
+    __shared__ PodS sp[HOT_CHUNK];
+    __shared__ u32 hi_s[HOT_WARPS][HOT_CHUNK], lo_s[HOT_WARPS][HOT_CHUNK];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u32 c0 = p_begin + blockIdx.y * HOT_CHUNK;
+    const u32 cn = min(HOT_CHUNK, p_end - c0);
+    for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) sp[i] = pods[c0 + i];
+    const u32 base = (blockIdx.x * HOT_WARPS + warp) * (NPL * 32);
+    NodeRegs<NPL, CLK> r;
+    hot_load_nodes(r, s, base, lane);
+    __syncthreads();
+    u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFFu, cur_m = 0;
+    u32 hi_l[NPL], lo_l[NPL], bound[NPL];
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) { hi_l[j] = 0; lo_l[j] = 0xFFFFFFFFu; bound[j] = 0; }
+    u32 hi_w = 0, lo_w = 0xFFFFFFFFu;
+    for (u32 i = 0; i < cn; ++i) {
+        const PodS pod = sp[i];
+        const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
+        if (pod.cls != cur_cls) hot_load_class(r, s, tables, pod.cls, base, lane);
+        cur_cls = pod.cls; cur_gid = pod.gid; cur_m = pod.m;
+        const u32 reqM = pod.req & 0xFFu, reqC = (pod.req >> 8) & 0xFFu;
+        bool any_miss = false;
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) {
+            if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
+                bool fit;
+                const u32 raw = hot_eval(r, j, pod.m, pod.c, pod.num, reqM, reqC, fit, bound[j]);
+                hi_l[j] = fit ? raw : 0u;
+                lo_l[j] = fit ? raw : 0xFFFFFFFFu;
+                any_miss = true;
+            }
+        }
+        if (any_miss) {
+            u32 hi = hi_l[0], lo = lo_l[0];
+#pragma unroll
+            for (int j = 1; j < NPL; ++j) { hi = max(hi, hi_l[j]); lo = min(lo, lo_l[j]); }
+            hi_w = __reduce_max_sync(0xFFFFFFFFu, hi);
+            lo_w = __reduce_min_sync(0xFFFFFFFFu, lo);
+        }
+        if (lane == 0) {
+            hi_s[warp][i] = hi_w;
+            lo_s[warp][i] = lo_w;
+        }
+    }
+    __syncthreads();
+    for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) {
+        u32 hi = 0, lo = 0xFFFFFFFFu;
+#pragma unroll
+        for (int w = 0; w < HOT_WARPS; ++w) {
+            hi = max(hi, hi_s[w][i]);
+            lo = min(lo, lo_s[w][i]);
+        }
+        if (lo != 0xFFFFFFFFu) {  // some node of this tile is feasible
+            const u32 orig = sp[i].orig;
+            atomicMax(&hilo[2 * (size_t)orig], (u64)hi);
+            atomicMax(&hilo[2 * (size_t)orig + 1], ~(u64)lo);
+        }
+    }
+}
+
+// rescale constants per sorted pod, from the (cross-shard reduced) lowest/highest
+__global__ void k_norm_prep(const PodS *__restrict__ pods, u32 P, const u64 *__restrict__ hilo, PodNrm *out) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const u32 orig = pods[i].orig;
+    PodNrm r;
+    if (hilo[2 * (size_t)orig + 1] == 0) {  // no feasible node anywhere
+        r.lo = 0; r.hi = 0xFFFFFFFFu; r.mhi = 0; r.mlo = 0;
+    } else {
+        const u32 hi = (u32)hilo[2 * (size_t)orig];
+        u32 lo = (u32)(~hilo[2 * (size_t)orig + 1]);
+        if (hi == lo) lo = lo - 1u;  // scheduler.go:147-149 (may become -1 = 0xFFFFFFFF)
+        const u32 d = hi - lo;       // 1 .. 2^25
+        const u64 M = ((1ull << 57) / d) + 1ull;
+        r.lo = lo; r.hi = hi; r.mhi = (u32)(M >> 32); r.mlo = (u32)M;
+    }
+    out[i] = r;
+}
+
+// output pass: feasible bits, Score (int64), NormalizeScore (uint8), feasible count, node choice
+template <int NPL, bool CLK, bool WRITE>
+__global__ void __launch_bounds__(HOT_THREADS) k_fast_out(DevSnap s, const PodS *__restrict__ pods, const PodNrm *__restrict__ nrm,
+                                                          u32 p_begin, u32 p_end, const u32 *__restrict__ tables, u64 *count, u64 *ckey,
+                                                          i64 *raw_out, u8 *norm_out, u32 *bits_out, u64 stride) {
+    __shared__ PodS sp[HOT_CHUNK];
+    __shared__ PodNrm sn[HOT_CHUNK];
+    __shared__ u32 cnt_s[HOT_WARPS][HOT_CHUNK];
+    __shared__ u32 best_s[HOT_WARPS][HOT_CHUNK];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u32 c0 = p_begin + blockIdx.y * HOT_CHUNK;
+    const u32 cn = min(HOT_CHUNK, p_end - c0);
+    for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) {
+        sp[i] = pods[c0 + i];
+        sn[i] = nrm[c0 + i];
+    }
+    const u32 base = (blockIdx.x * HOT_WARPS + warp) * (NPL * 32);
+    NodeRegs<NPL, CLK> r;
+    hot_load_nodes(r, s, base, lane);
+    __syncthreads();
+    u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFFu, cur_m = 0;
+    u32 raw_l[NPL], bound[NPL], fitmask[NPL];
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) { raw_l[j] = 0; bound[j] = 0; fitmask[j] = 0; }
+    u32 cnt = 0;
+    for (u32 i = 0; i < cn; ++i) {
+        const PodS pod = sp[i];
+        const PodNrm pn = sn[i];
+        const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
+        if (pod.cls != cur_cls) hot_load_class(r, s, tables, pod.cls, base, lane);
+        cur_cls = pod.cls; cur_gid = pod.gid; cur_m = pod.m;
+        const u32 reqM = pod.req & 0xFFu, reqC = (pod.req >> 8) & 0xFFu;
+        bool any_miss = false;
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) {
+            if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
+                bool fit;
+                raw_l[j] = hot_eval(r, j, pod.m, pod.c, pod.num, reqM, reqC, fit, bound[j]);
+                fitmask[j] = __ballot_sync(0xFFFFFFFFu, fit);
+                any_miss = true;
+            }
+        }
+        if (any_miss) {
+            cnt = 0;
+#pragma unroll
+            for (int j = 0; j < NPL; ++j) cnt += __popc(fitmask[j]);
+        }
+        u32 best = 0xFFFFFFFFu;
+        const size_t row = (size_t)pod.orig * stride;
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) {
+            const bool fit = (fitmask[j] >> lane) & 1u;
+            const u32 raw = raw_l[j];
+            const u32 topmask = __ballot_sync(0xFFFFFFFFu, fit && raw == pn.hi);
+            if (topmask && best == 0xFFFFFFFFu) best = base + j * 32 + (__ffs(topmask) - 1);
+            if (WRITE) {
+                const u32 n = base + j * 32 + lane;
+                // scheduler.go:152: (raw - lo) * 100 / (hi - lo), exact via the 57-bit reciprocal
+                const u32 x = (raw - pn.lo) * 100u;
+                const u32 t = __umulhi(x, pn.mlo);
+                const u32 q = (x * pn.mhi + t) >> 25;
+                if (n < s.n_nodes) {
+                    raw_out[row + n] = (i64)raw;   // filter.go:84-86 is the identity below 2^63
+                    norm_out[row + n] = fit ? (u8)q : (u8)0;
+                }
+                if (lane == 0 && base + j * 32 < stride) bits_out[(size_t)pod.orig * (stride / 32) + ((base + j * 32) >> 5)] = fitmask[j];
+            }
+        }
+        if (lane == 0) {
+            cnt_s[warp][i] = cnt;
+            best_s[warp][i] = best;
+        }
+    }
+    __syncthreads();
+    for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) {
+        u32 cnt2 = 0, best = 0xFFFFFFFFu;
+#pragma unroll
+        for (int w = 0; w < HOT_WARPS; ++w) {
+            cnt2 += cnt_s[w][i];
+            best = min(best, best_s[w][i]);
+        }
+        const u32 orig = sp[i].orig;
+        if (cnt2) atomicAdd(&count[orig], (u64)cnt2);
+        if (best != 0xFFFFFFFFu) atomicMax(&ckey[orig], ckey_of(s.node_base + best));
+    }
+}

@@ -12,8 +12,11 @@
 #include <string>
 #include <vector>
 
+#include <cub/device/device_radix_sort.cuh>  // library utility: orders the (<= few 100k) pod keys, off the hot path
+
 #include "common.cuh"
 #include "direct_kernels.cuh"
+#include "fast_kernels.cuh"
 
 // ------------------------------------------------------------------------------------------
 // errors
@@ -125,7 +128,26 @@ struct yoda_ctx {
     u32 list_cap = 0;
     // NCCL
     ncclComm_t comm = nullptr;
+    // fast (narrow) path workspace
+    int ph_path = 0;  // path of the evaluation in flight: 0 direct, 1 fast
+    u32 fw_pods_cap = 0, fw_htab = 0;
+    u64 *fw_gkeys = nullptr, *fw_ckeys = nullptr;
+    u32 *fw_gids = nullptr, *fw_cids = nullptr, *fw_crep = nullptr, *fw_slot = nullptr, *fw_pod_gid = nullptr;
+    u64 *fw_keys_in = nullptr, *fw_keys_out = nullptr;
+    u32 *fw_vals_in = nullptr, *fw_vals_out = nullptr;
+    void *fw_cub_tmp = nullptr;
+    size_t fw_cub_bytes = 0;
+    GroupDesc *fw_gdesc = nullptr;
+    PodS *fw_pods = nullptr;
+    PodNrm *fw_nrm = nullptr;
+    u32 *fw_m_sorted = nullptr, *fw_step = nullptr, *fw_cls_max = nullptr, *fw_tables = nullptr;
+    u32 fw_tables_classes = 0;
+    FastCtl *fw_ctl = nullptr, *fw_hctl = nullptr;
+    u32 fw_n_groups = 0, fw_n_classes = 0, fw_p0 = 0;
 };
+
+#define FAST_CLASS_CAP 4096u
+#define FAST_TABLE_BYTES (1ull << 30)
 
 struct DeviceGuard {
     int prev = -1;
@@ -203,8 +225,7 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
     if (!rc) rc = dev_alloc(&s.alloc_sum, cap);
     if (!rc) rc = dev_alloc(&s.stat, cap);
     if (!rc) rc = dev_alloc(&s.meta, cap);
-    if (!rc) rc = dev_alloc(&s.free32, (size_t)cap * G);
-    if (!rc) rc = dev_alloc(&s.clock32, (size_t)cap * G);
+    for (int f = 0; f < NFIELD && !rc; ++f) rc = dev_alloc(&s.n32[f], (size_t)cap * G);
     if (!rc) rc = dev_alloc(&s.cardnum32, cap);
     if (!rc) rc = dev_alloc(&s.stat32, cap);
     if (!rc) rc = dev_alloc(&c->d_wide_flag, 1);
@@ -236,12 +257,19 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     DevSnap &s = c->snap;
     for (int f = 0; f < NFIELD; ++f) dev_free(s.f[f]);
     dev_free(s.card_number); dev_free(s.free_sum); dev_free(s.total_sum); dev_free(s.alloc_sum);
-    dev_free(s.stat); dev_free(s.meta); dev_free(s.free32); dev_free(s.clock32);
+    dev_free(s.stat); dev_free(s.meta);
+    for (int f = 0; f < NFIELD; ++f) dev_free(s.n32[f]);
     dev_free(s.cardnum32); dev_free(s.stat32);
     dev_free(c->d_wide_flag); dev_free(c->d_lohi); dev_free(c->d_list); dev_free(c->d_upd);
     dev_free(c->d_req); dev_free(c->d_pods); dev_free(c->d_max6); dev_free(c->d_count);
     dev_free(c->d_hilo); dev_free(c->d_ckey); dev_free(c->d_res);
     dev_free(c->d_raw); dev_free(c->d_norm); dev_free(c->d_bits);
+    dev_free(c->fw_gkeys); dev_free(c->fw_ckeys); dev_free(c->fw_gids); dev_free(c->fw_cids); dev_free(c->fw_crep);
+    dev_free(c->fw_slot); dev_free(c->fw_pod_gid); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
+    dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_gdesc); dev_free(c->fw_pods); dev_free(c->fw_nrm);
+    dev_free(c->fw_m_sorted); dev_free(c->fw_step); dev_free(c->fw_cls_max); dev_free(c->fw_tables); dev_free(c->fw_ctl);
+    if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
+    if (c->fw_hctl) cudaFreeHost(c->fw_hctl);
     if (c->h_upd) cudaFreeHost(c->h_upd);
     if (c->h_req) cudaFreeHost(c->h_req);
     if (c->h_res) cudaFreeHost(c->h_res);
@@ -445,9 +473,224 @@ static int ensure_matrices(yoda_ctx *c, u32 P, u64 stride) {
         (c)->launches++;     \
     } while (0)
 
-// phase 0: canonical pods, identities, local maxima + feasible counts
-static int phase0(yoda_ctx *c, const yoda_pod_req *d_req) {
+// ---- fast path workspace ------------------------------------------------------------------
+static u32 fast_class_cap(const yoda_ctx *c) {
+    const u64 per_class = (u64)c->snap.cap * G * sizeof(u32);
+    return (u32)std::max<u64>(1, std::min<u64>(FAST_CLASS_CAP, FAST_TABLE_BYTES / per_class));
+}
+
+static int ensure_fast(yoda_ctx *c, u32 P) {
+    if (!c->fw_ctl) {
+        TRY(dev_alloc(&c->fw_ctl, 1));
+        if (cudaMallocHost((void **)&c->fw_hctl, sizeof(FastCtl)) != cudaSuccess) return fail(YODA_E_NOMEM, "cudaMallocHost failed");
+        TRY(dev_alloc(&c->fw_gdesc, FAST_GROUP_CAP));
+        TRY(dev_alloc(&c->fw_cls_max, (size_t)FAST_CLASS_CAP * 6));
+    }
+    if (P <= c->fw_pods_cap) return YODA_OK;
+    CU(cudaStreamSynchronize(c->stream));
+    const u32 cap = c->pods_cap;  // grown by ensure_pods just before
+    u32 htab = 1024;
+    while (htab < 2 * cap) htab <<= 1;
+    dev_free(c->fw_gkeys); dev_free(c->fw_ckeys); dev_free(c->fw_gids); dev_free(c->fw_cids); dev_free(c->fw_crep);
+    dev_free(c->fw_slot); dev_free(c->fw_pod_gid); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
+    dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_pods); dev_free(c->fw_nrm);
+    dev_free(c->fw_m_sorted); dev_free(c->fw_step);
+    if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
+    c->fw_cub_tmp = nullptr;
+    c->fw_pods_cap = 0;
+    TRY(dev_alloc(&c->fw_gkeys, htab));
+    TRY(dev_alloc(&c->fw_ckeys, htab));
+    TRY(dev_alloc(&c->fw_gids, htab));
+    TRY(dev_alloc(&c->fw_cids, htab));
+    TRY(dev_alloc(&c->fw_crep, htab));
+    TRY(dev_alloc(&c->fw_slot, cap));
+    TRY(dev_alloc(&c->fw_pod_gid, cap));
+    TRY(dev_alloc(&c->fw_keys_in, cap));
+    TRY(dev_alloc(&c->fw_keys_out, cap));
+    TRY(dev_alloc(&c->fw_vals_in, cap));
+    TRY(dev_alloc(&c->fw_vals_out, cap));
+    TRY(dev_alloc(&c->fw_pods, cap));
+    TRY(dev_alloc(&c->fw_nrm, cap));
+    TRY(dev_alloc(&c->fw_m_sorted, cap));
+    TRY(dev_alloc(&c->fw_step, (size_t)cap * 6));
+    size_t bytes = 0;
+    CU(cub::DeviceRadixSort::SortPairs(nullptr, bytes, c->fw_keys_in, c->fw_keys_out, c->fw_vals_in, c->fw_vals_out, (int)cap, 0,
+                                       33 + FAST_GID_BITS, c->stream));
+    if (cudaMalloc(&c->fw_cub_tmp, std::max<size_t>(bytes, 16)) != cudaSuccess) return fail(YODA_E_NOMEM, "sort scratch allocation failed");
+    c->fw_cub_bytes = bytes;
+    c->fw_htab = htab;
+    c->fw_pods_cap = cap;
+    return YODA_OK;
+}
+
+static int fast_read_ctl(yoda_ctx *c) {
+    CU(cudaMemcpyAsync(c->fw_hctl, c->fw_ctl, sizeof(FastCtl), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return YODA_OK;
+}
+
+// ---- direct path bodies ---------------------------------------------------------------------
+static int direct_pods_launch(yoda_ctx *c, int mode) {
     const u32 P = c->ph_P, N = c->snap.n_nodes;
+    if (!N) return YODA_OK;
+    const u32 gx = (P + DPT - 1) / DPT;
+    u32 chunks = std::max(1u, std::min((N + DTN - 1) / DTN, (592u + gx - 1) / gx));
+    chunks = std::min(chunks, 65535u);
+    const u32 npc = round_up((N + chunks - 1) / chunks, DTN);
+    dim3 grid(gx, (N + npc - 1) / npc);
+    if (mode == 0)
+        k_direct_pods<0><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo);
+    else
+        k_direct_pods<1><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo);
+    LAUNCHED(c);
+    return YODA_OK;
+}
+
+static int direct_out_launch(yoda_ctx *c) {
+    const u32 P = c->ph_P, N = c->snap.n_nodes;
+    if (!N) return YODA_OK;
+    cudaStream_t st = c->stream;
+    const bool full = (c->ph_flags & YODA_EVAL_FULL) != 0;
+    const u32 gx = (N + DCT - 1) / DCT;
+    const u32 want_y = std::max(1u, 2368u / gx);
+    u32 ppc = std::max(1u, (P + want_y - 1) / want_y);
+    ppc = std::min(ppc, 64u);
+    ppc = std::max(ppc, (P + 65534u) / 65535u);
+    dim3 grid(gx, (P + ppc - 1) / ppc);
+    if (full)
+        k_direct_out<true><<<grid, DCT, 0, st>>>(c->snap, c->d_pods, P, ppc, c->d_max6, c->d_count, c->d_hilo, c->d_ckey, c->d_raw,
+                                                 c->d_norm, c->d_bits, c->stride);
+    else
+        k_direct_out<false><<<grid, DCT, 0, st>>>(c->snap, c->d_pods, P, ppc, c->d_max6, c->d_count, c->d_hilo, c->d_ckey, nullptr,
+                                                  nullptr, nullptr, c->stride);
+    LAUNCHED(c);
+    return YODA_OK;
+}
+
+// ---- fast path bodies -------------------------------------------------------------------------
+// groups -> sorted pods -> maxima.  Returns with ph_path = 0 if the batch has too many groups.
+static int fast_phase0(yoda_ctx *c) {
+    const u32 P = c->ph_P, N = c->snap.n_nodes;
+    cudaStream_t st = c->stream;
+    const u32 pb = (P + 255) / 256;
+    const FastCtl init = {0, 0, P, 0};
+    *c->fw_hctl = init;
+    CU(cudaMemcpyAsync(c->fw_ctl, c->fw_hctl, sizeof(FastCtl), cudaMemcpyHostToDevice, st));
+    k_hash_clear<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_gkeys, c->fw_gids, c->fw_htab);
+    LAUNCHED(c);
+    k_group_insert<<<pb, 256, 0, st>>>(c->d_pods, P, c->fw_gkeys, c->fw_htab - 1, c->fw_slot);
+    LAUNCHED(c);
+    k_hash_compact<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_gkeys, c->fw_gids, c->fw_htab, &c->fw_ctl->n_groups);
+    LAUNCHED(c);
+    TRY(fast_read_ctl(c));
+    c->fw_n_groups = c->fw_hctl->n_groups;
+    if (c->fw_n_groups > FAST_GROUP_CAP) {
+        c->ph_path = 0;
+        return YODA_OK;
+    }
+    k_group_assign<<<pb, 256, 0, st>>>(c->d_pods, P, c->fw_slot, c->fw_gids, c->fw_gdesc, FAST_GROUP_CAP, c->fw_keys_in, c->fw_vals_in,
+                                       c->fw_pod_gid, c->fw_ctl);
+    LAUNCHED(c);
+    size_t bytes = c->fw_cub_bytes;
+    CU(cub::DeviceRadixSort::SortPairs(c->fw_cub_tmp, bytes, c->fw_keys_in, c->fw_keys_out, c->fw_vals_in, c->fw_vals_out, (int)P, 0,
+                                       33 + FAST_GID_BITS, st));
+    c->launches += 6;  // cub radix sort passes (library kernels)
+    k_build_sorted<<<pb, 256, 0, st>>>(c->d_pods, P, c->fw_keys_out, c->fw_vals_out, c->fw_gdesc, FAST_GROUP_CAP, c->fw_pods,
+                                       c->fw_m_sorted, c->fw_ctl);
+    LAUNCHED(c);
+    CU(cudaEventRecord(c->ev[EV_PREP], st));
+    CU(cudaMemsetAsync(c->fw_step, 0, (size_t)P * 6 * sizeof(u32), st));
+    if (N) {
+        dim3 grid((N + MAXT - 1) / MAXT, c->fw_n_groups);
+        k_max_thresholds<<<grid, MAXT, 0, st>>>(c->snap, c->fw_gdesc, c->fw_n_groups, c->fw_m_sorted, c->fw_step, P);
+        LAUNCHED(c);
+    }
+    k_max_scan<<<c->fw_n_groups, SCANT, 0, st>>>(c->fw_gdesc, c->fw_n_groups, c->fw_step, c->fw_pods, c->d_max6, P);
+    LAUNCHED(c);
+    return YODA_OK;
+}
+
+template <bool CLK>
+static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
+    if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
+    constexpr int NPL = CLK ? 2 : 4;
+    dim3 grid((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (p_end - p_begin + HOT_CHUNK - 1) / HOT_CHUNK);
+    k_fast_score<NPL, CLK><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo);
+    LAUNCHED(c);
+    return YODA_OK;
+}
+
+template <bool CLK>
+static int fast_out_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
+    if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
+    constexpr int NPL = CLK ? 2 : 4;
+    dim3 grid((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (p_end - p_begin + HOT_CHUNK - 1) / HOT_CHUNK);
+    if (c->ph_flags & YODA_EVAL_FULL)
+        k_fast_out<NPL, CLK, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->fw_nrm, p_begin, p_end, c->fw_tables,
+                                                                        c->d_count, c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride);
+    else
+        k_fast_out<NPL, CLK, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->fw_nrm, p_begin, p_end, c->fw_tables,
+                                                                         c->d_count, c->d_ckey, nullptr, nullptr, nullptr, c->stride);
+    LAUNCHED(c);
+    return YODA_OK;
+}
+
+// classes -> tables -> score reduce.  Returns with ph_path = 0 if the batch cannot use the tables.
+static int fast_phase1(yoda_ctx *c) {
+    const u32 P = c->ph_P, N = c->snap.n_nodes;
+    cudaStream_t st = c->stream;
+    const u32 pb = (P + 255) / 256;
+    const u32 ccap = fast_class_cap(c);
+    k_hash_clear<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_ckeys, c->fw_crep, c->fw_htab);
+    LAUNCHED(c);
+    k_class_insert<<<pb, 256, 0, st>>>(c->fw_pods, P, c->d_max6, c->fw_ckeys, c->fw_htab - 1, c->fw_crep, c->fw_slot);
+    LAUNCHED(c);
+    k_hash_compact<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_ckeys, c->fw_cids, c->fw_htab, &c->fw_ctl->n_classes);
+    LAUNCHED(c);
+    k_class_assign<<<pb, 256, 0, st>>>(c->fw_pods, P, c->d_max6, c->fw_crep, c->fw_cids, c->fw_slot, c->fw_cls_max, ccap, c->fw_ctl);
+    LAUNCHED(c);
+    TRY(fast_read_ctl(c));
+    c->fw_n_classes = c->fw_hctl->n_classes;
+    c->fw_p0 = std::min(c->fw_hctl->p0, P);
+    if (c->fw_hctl->err || c->fw_n_classes > ccap) {
+        c->ph_path = 0;
+        return YODA_OK;
+    }
+    if (c->fw_n_classes > c->fw_tables_classes) {
+        dev_free(c->fw_tables);
+        c->fw_tables_classes = 0;
+        const u32 want = std::min(ccap, std::max(c->fw_n_classes * 2, 64u));
+        TRY(dev_alloc(&c->fw_tables, (size_t)want * c->snap.cap * G));
+        c->fw_tables_classes = want;
+    }
+    if (N) {
+        dim3 grid((N + CLST - 1) / CLST, c->fw_n_classes);
+        k_class_tables<<<grid, CLST, 0, st>>>(c->snap, c->fw_cls_max, c->fw_n_classes, c->fw_tables, c->fw_ctl);
+        LAUNCHED(c);
+    }
+    TRY(fast_read_ctl(c));
+    if (c->fw_hctl->err) {
+        c->ph_path = 0;
+        return YODA_OK;
+    }
+    TRY(fast_score_launch<false>(c, 0, c->fw_p0));
+    TRY(fast_score_launch<true>(c, c->fw_p0, P));
+    return YODA_OK;
+}
+
+static int fast_phase2(yoda_ctx *c) {
+    const u32 P = c->ph_P;
+    k_norm_prep<<<(P + 255) / 256, 256, 0, c->stream>>>(c->fw_pods, P, c->d_hilo, c->fw_nrm);
+    LAUNCHED(c);
+    TRY(fast_out_launch<false>(c, 0, c->fw_p0));
+    TRY(fast_out_launch<true>(c, c->fw_p0, P));
+    return YODA_OK;
+}
+
+// ---- phases ---------------------------------------------------------------------------------
+// phase 0: canonical pods, identities, local maxima (collection.CollectMaxValues)
+static int phase0(yoda_ctx *c, const yoda_pod_req *d_req) {
+    const u32 P = c->ph_P;
     cudaStream_t st = c->stream;
     c->launches = 0;
     CU(cudaEventRecord(c->ev[EV_START], st));
@@ -455,15 +698,10 @@ static int phase0(yoda_ctx *c, const yoda_pod_req *d_req) {
     LAUNCHED(c);
     k_init_partials<<<(P + 255) / 256, 256, 0, st>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, P);
     LAUNCHED(c);
-    CU(cudaEventRecord(c->ev[EV_PREP], st));
-    if (N) {
-        const u32 gx = (P + DPT - 1) / DPT;
-        u32 chunks = std::max(1u, std::min((N + DTN - 1) / DTN, (592u + gx - 1) / gx));
-        chunks = std::min(chunks, 65535u);
-        const u32 npc = round_up((N + chunks - 1) / chunks, DTN);
-        dim3 grid(gx, (N + npc - 1) / npc);
-        k_direct_pods<0><<<grid, DPT, 0, st>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_count, c->d_hilo);
-        LAUNCHED(c);
+    if (c->ph_path == 1) TRY(fast_phase0(c));
+    if (c->ph_path == 0) {
+        CU(cudaEventRecord(c->ev[EV_PREP], st));
+        TRY(direct_pods_launch(c, 0));
     }
     CU(cudaEventRecord(c->ev[EV_MAX], st));
     return YODA_OK;
@@ -471,42 +709,16 @@ static int phase0(yoda_ctx *c, const yoda_pod_req *d_req) {
 
 // phase 1: local lowest/highest over feasible nodes
 static int phase1(yoda_ctx *c) {
-    const u32 P = c->ph_P, N = c->snap.n_nodes;
-    cudaStream_t st = c->stream;
-    if (N) {
-        const u32 gx = (P + DPT - 1) / DPT;
-        u32 chunks = std::max(1u, std::min((N + DTN - 1) / DTN, (592u + gx - 1) / gx));
-        chunks = std::min(chunks, 65535u);
-        const u32 npc = round_up((N + chunks - 1) / chunks, DTN);
-        dim3 grid(gx, (N + npc - 1) / npc);
-        k_direct_pods<1><<<grid, DPT, 0, st>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_count, c->d_hilo);
-        LAUNCHED(c);
-    }
-    CU(cudaEventRecord(c->ev[EV_SCORE], st));
+    if (c->ph_path == 1) TRY(fast_phase1(c));
+    if (c->ph_path == 0) TRY(direct_pods_launch(c, 1));
+    CU(cudaEventRecord(c->ev[EV_SCORE], c->stream));
     return YODA_OK;
 }
 
-// phase 2: output pass (matrices when FULL) + node choice
+// phase 2: output pass (matrices when FULL), feasible counts, node choice
 static int phase2(yoda_ctx *c) {
-    const u32 P = c->ph_P, N = c->snap.n_nodes;
-    cudaStream_t st = c->stream;
-    const bool full = (c->ph_flags & YODA_EVAL_FULL) != 0;
-    if (N) {
-        const u32 gx = (N + DCT - 1) / DCT;
-        const u32 want_y = std::max(1u, 2368u / gx);
-        u32 ppc = std::max(1u, (P + want_y - 1) / want_y);
-        ppc = std::min(ppc, 64u);
-        ppc = std::max(ppc, (P + 65534u) / 65535u);
-        dim3 grid(gx, (P + ppc - 1) / ppc);
-        if (full)
-            k_direct_out<true><<<grid, DCT, 0, st>>>(c->snap, c->d_pods, P, ppc, c->d_max6, c->d_count, c->d_hilo, c->d_ckey,
-                                                     c->d_raw, c->d_norm, c->d_bits, c->stride);
-        else
-            k_direct_out<false><<<grid, DCT, 0, st>>>(c->snap, c->d_pods, P, ppc, c->d_max6, c->d_count, c->d_hilo, c->d_ckey,
-                                                      nullptr, nullptr, nullptr, c->stride);
-        LAUNCHED(c);
-    }
-    return YODA_OK;
+    if (c->ph_path == 1) return fast_phase2(c);
+    return direct_out_launch(c);
 }
 
 static int phase3(yoda_ctx *c) {
@@ -523,6 +735,8 @@ static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
     TRY(ensure_pods(c, P));
     c->stride = round_up(std::max(c->snap.n_nodes, 1u), 128);
     if (flags & YODA_EVAL_FULL) TRY(ensure_matrices(c, P, c->stride));
+    c->ph_path = (c->narrow_ok && !(flags & YODA_EVAL_FORCE_DIRECT)) ? 1 : 0;
+    if (c->ph_path == 1) TRY(ensure_fast(c, P));
     c->ph_P = P;
     c->ph_flags = flags;
     c->ph_done = -1;
@@ -535,14 +749,14 @@ static int exchange_locked(yoda_ctx *c, int phase) {
     if (!c->comm) return YODA_OK;
     const u32 P = c->ph_P;
     if (phase == 0) {
-        NC(g_nccl.GroupStart());
         NC(g_nccl.AllReduce(c->d_max6, c->d_max6, (size_t)P * 6, ncclUint64, ncclMax, c->comm, c->stream));
-        NC(g_nccl.AllReduce(c->d_count, c->d_count, P, ncclUint64, ncclSum, c->comm, c->stream));
-        NC(g_nccl.GroupEnd());
     } else if (phase == 1) {
         NC(g_nccl.AllReduce(c->d_hilo, c->d_hilo, (size_t)P * 2, ncclUint64, ncclMax, c->comm, c->stream));
     } else if (phase == 2) {
+        NC(g_nccl.GroupStart());
         NC(g_nccl.AllReduce(c->d_ckey, c->d_ckey, P, ncclUint64, ncclMax, c->comm, c->stream));
+        NC(g_nccl.AllReduce(c->d_count, c->d_count, P, ncclUint64, ncclSum, c->comm, c->stream));
+        NC(g_nccl.GroupEnd());
     }
     return YODA_OK;
 }
@@ -560,7 +774,9 @@ static void collect_timing(yoda_ctx *c, bool copies) {
         cudaEventElapsedTime(&t.d2h_ms, c->ev[EV_D2H0], c->ev[EV_D2H1]);
     }
     t.kernels = c->launches;
-    t.path = 0;
+    t.path = (u32)c->ph_path;
+    t.n_classes = c->ph_path ? c->fw_n_classes : 0;
+    t.n_groups = c->ph_path ? c->fw_n_groups : 0;
     cudaGetLastError();
 }
 
@@ -707,11 +923,11 @@ extern "C" int yoda_phase_exchange(yoda_ctx *c, int phase, yoda_xchg *bufs, int 
     };
     if (phase == 0) {
         put(c->d_max6, P * 6, YODA_XCHG_MAX);
-        put(c->d_count, P, YODA_XCHG_SUM);
     } else if (phase == 1) {
         put(c->d_hilo, P * 2, YODA_XCHG_MAX);
     } else if (phase == 2) {
         put(c->d_ckey, P, YODA_XCHG_MAX);
+        put(c->d_count, P, YODA_XCHG_SUM);
     }
     if (k > *n_bufs) return fail(YODA_E_RANGE, "need %d exchange descriptors", k);
     *n_bufs = k;
