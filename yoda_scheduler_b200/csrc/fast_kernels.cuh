@@ -454,18 +454,30 @@ __device__ __forceinline__ u32 hot_eval(const NodeRegs<NPL, CLK> &r, int j, u32 
 // The pods arrive sorted by (group, memory).  Along that order the verdict and score of a node
 // change only when the memory value crosses one of the node's FreeMemory values, so each lane
 // keeps its last result and the bound up to which it stays valid; a 32-node slot is re-evaluated
-// only when one of its lanes crossed its bound (or the group/class changed).
+// only when one of its lanes crossed its bound (or the group/class changed).  Within a group the
+// memory values ascend, so a node that stopped fitting never fits again: its bound becomes +inf.
+
+struct PodRegs {
+    u32 m, c, num, reqM, reqC, cls, orig, gid;
+};
+__device__ __forceinline__ PodRegs pod_from_smem(const uint4 *sp, u32 i) {
+    const uint4 a = sp[2 * i], b = sp[2 * i + 1];  // PodS: m c num req | cls orig gid pad
+    PodRegs p;
+    p.m = a.x; p.c = a.y; p.num = a.z; p.reqM = a.w & 0xFFu; p.reqC = (a.w >> 8) & 0xFFu;
+    p.cls = b.x; p.orig = b.y; p.gid = b.z;
+    return p;
+}
 
 // score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145)
 template <int NPL, bool CLK>
 __global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
                                                             const u32 *__restrict__ tables, u64 *hilo) {
-    __shared__ PodS sp[HOT_CHUNK];
+    __shared__ uint4 sp[HOT_CHUNK * 2];
     __shared__ u32 hi_s[HOT_WARPS][HOT_CHUNK], lo_s[HOT_WARPS][HOT_CHUNK];
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const u32 c0 = p_begin + blockIdx.y * HOT_CHUNK;
     const u32 cn = min(HOT_CHUNK, p_end - c0);
-    for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) sp[i] = pods[c0 + i];
+    for (u32 i = threadIdx.x; i < cn * 2; i += HOT_THREADS) sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
     const u32 base = (blockIdx.x * HOT_WARPS + warp) * (NPL * 32);
     NodeRegs<NPL, CLK> r;
     hot_load_nodes(r, s, base, lane);
@@ -476,17 +488,18 @@ __global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const Pod
     for (int j = 0; j < NPL; ++j) { hi_l[j] = 0; lo_l[j] = 0xFFFFFFFFu; bound[j] = 0; }
     u32 hi_w = 0, lo_w = 0xFFFFFFFFu;
     for (u32 i = 0; i < cn; ++i) {
-        const PodS pod = sp[i];
+        const PodRegs pod = pod_from_smem(sp, i);
         const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
         if (pod.cls != cur_cls) hot_load_class(r, s, tables, pod.cls, base, lane);
         cur_cls = pod.cls; cur_gid = pod.gid; cur_m = pod.m;
-        const u32 reqM = pod.req & 0xFFu, reqC = (pod.req >> 8) & 0xFFu;
         bool any_miss = false;
 #pragma unroll
         for (int j = 0; j < NPL; ++j) {
             if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
                 bool fit;
-                const u32 raw = hot_eval(r, j, pod.m, pod.c, pod.num, reqM, reqC, fit, bound[j]);
+                u32 b;
+                const u32 raw = hot_eval(r, j, pod.m, pod.c, pod.num, pod.reqM, pod.reqC, fit, b);
+                bound[j] = fit ? b : 0xFFFFFFFFu;
                 hi_l[j] = fit ? raw : 0u;
                 lo_l[j] = fit ? raw : 0xFFFFFFFFu;
                 any_miss = true;
@@ -513,7 +526,7 @@ __global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const Pod
             lo = min(lo, lo_s[w][i]);
         }
         if (lo != 0xFFFFFFFFu) {  // some node of this tile is feasible
-            const u32 orig = sp[i].orig;
+            const u32 orig = sp[2 * i + 1].y;
             atomicMax(&hilo[2 * (size_t)orig], (u64)hi);
             atomicMax(&hilo[2 * (size_t)orig + 1], ~(u64)lo);
         }
@@ -539,72 +552,92 @@ __global__ void k_norm_prep(const PodS *__restrict__ pods, u32 P, const u64 *__r
     out[i] = r;
 }
 
-// output pass: feasible bits, Score (int64), NormalizeScore (uint8), feasible count, node choice
+// output pass: feasible bits, Score (int64), NormalizeScore (uint8), feasible count, node choice.
+// Rows are padded to the CTA tile (stride % (HOT_WARPS*NPL*32) == 0), so no lane is out of range:
+// lanes past the last node hold no SCV, score 0 and write into the padding.
 template <int NPL, bool CLK, bool WRITE>
 __global__ void __launch_bounds__(HOT_THREADS) k_fast_out(DevSnap s, const PodS *__restrict__ pods, const PodNrm *__restrict__ nrm,
                                                           u32 p_begin, u32 p_end, const u32 *__restrict__ tables, u64 *count, u64 *ckey,
                                                           i64 *raw_out, u8 *norm_out, u32 *bits_out, u64 stride) {
-    __shared__ PodS sp[HOT_CHUNK];
-    __shared__ PodNrm sn[HOT_CHUNK];
+    __shared__ uint4 sp[HOT_CHUNK * 2];
+    __shared__ uint4 sn[HOT_CHUNK];
     __shared__ u32 cnt_s[HOT_WARPS][HOT_CHUNK];
     __shared__ u32 best_s[HOT_WARPS][HOT_CHUNK];
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const u32 c0 = p_begin + blockIdx.y * HOT_CHUNK;
     const u32 cn = min(HOT_CHUNK, p_end - c0);
-    for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) {
-        sp[i] = pods[c0 + i];
-        sn[i] = nrm[c0 + i];
-    }
+    for (u32 i = threadIdx.x; i < cn * 2; i += HOT_THREADS) sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
+    for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) sn[i] = reinterpret_cast<const uint4 *>(nrm + c0)[i];
     const u32 base = (blockIdx.x * HOT_WARPS + warp) * (NPL * 32);
     NodeRegs<NPL, CLK> r;
     hot_load_nodes(r, s, base, lane);
     __syncthreads();
-    u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFFu, cur_m = 0;
-    u32 raw_l[NPL], bound[NPL], fitmask[NPL];
+    u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFFu, cur_m = 0, cur_lo = 0, cur_hi = 0;
+    u64 raw64[NPL];                 // Score as stored (int64, high word 0)
+    u32 bound[NPL], fitm[NPL];      // validity bound per lane; feasible lanes of the slot (warp-uniform)
+    u32 fitl[NPL], qn[NPL], rmax[NPL];  // lane mask (0 / ~0), normalized score, best feasible score of the slot
 #pragma unroll
-    for (int j = 0; j < NPL; ++j) { raw_l[j] = 0; bound[j] = 0; fitmask[j] = 0; }
+    for (int j = 0; j < NPL; ++j) { raw64[j] = 0; bound[j] = 0; fitm[j] = 0; fitl[j] = 0; qn[j] = 0; rmax[j] = 0; }
     u32 cnt = 0;
+    unsigned long long *rawp = reinterpret_cast<unsigned long long *>(raw_out) + base + lane;
+    u8 *normp = norm_out + base + lane;
+    u32 *bitsp = bits_out + (base >> 5);
     for (u32 i = 0; i < cn; ++i) {
-        const PodS pod = sp[i];
-        const PodNrm pn = sn[i];
+        const PodRegs pod = pod_from_smem(sp, i);
+        const uint4 pn = sn[i];  // lo, hi, mhi, mlo
         const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
+        const bool nsame = same && (pn.x == cur_lo) && (pn.y == cur_hi);
         if (pod.cls != cur_cls) hot_load_class(r, s, tables, pod.cls, base, lane);
-        cur_cls = pod.cls; cur_gid = pod.gid; cur_m = pod.m;
-        const u32 reqM = pod.req & 0xFFu, reqC = (pod.req >> 8) & 0xFFu;
+        cur_cls = pod.cls; cur_gid = pod.gid; cur_m = pod.m; cur_lo = pn.x; cur_hi = pn.y;
         bool any_miss = false;
 #pragma unroll
         for (int j = 0; j < NPL; ++j) {
-            if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
+            const bool miss = !same || __any_sync(0xFFFFFFFFu, pod.m > bound[j]);
+            if (miss) {
                 bool fit;
-                raw_l[j] = hot_eval(r, j, pod.m, pod.c, pod.num, reqM, reqC, fit, bound[j]);
-                fitmask[j] = __ballot_sync(0xFFFFFFFFu, fit);
+                u32 b;
+                const u32 raw = hot_eval(r, j, pod.m, pod.c, pod.num, pod.reqM, pod.reqC, fit, b);
+                bound[j] = fit ? b : 0xFFFFFFFFu;
+                raw64[j] = raw;  // filter.go:84-86 is the identity below 2^63
+                fitm[j] = __ballot_sync(0xFFFFFFFFu, fit);
+                fitl[j] = fit ? 0xFFFFFFFFu : 0u;
+                rmax[j] = __reduce_max_sync(0xFFFFFFFFu, fit ? raw : 0u);
                 any_miss = true;
+            }
+            if (WRITE && (miss || !nsame)) {
+                // scheduler.go:152: (raw - lo) * 100 / (hi - lo), exact via the 57-bit reciprocal
+                const u32 x = ((u32)raw64[j] - pn.x) * 100u;
+                const u32 t = __umulhi(x, pn.w);
+                qn[j] = ((x * pn.z + t) >> 25) & fitl[j];
             }
         }
         if (any_miss) {
             cnt = 0;
 #pragma unroll
-            for (int j = 0; j < NPL; ++j) cnt += __popc(fitmask[j]);
+            for (int j = 0; j < NPL; ++j) cnt += __popc(fitm[j]);
         }
         u32 best = 0xFFFFFFFFu;
-        const size_t row = (size_t)pod.orig * stride;
 #pragma unroll
-        for (int j = 0; j < NPL; ++j) {
-            const bool fit = (fitmask[j] >> lane) & 1u;
-            const u32 raw = raw_l[j];
-            const u32 topmask = __ballot_sync(0xFFFFFFFFu, fit && raw == pn.hi);
-            if (topmask && best == 0xFFFFFFFFu) best = base + j * 32 + (__ffs(topmask) - 1);
-            if (WRITE) {
-                const u32 n = base + j * 32 + lane;
-                // scheduler.go:152: (raw - lo) * 100 / (hi - lo), exact via the 57-bit reciprocal
-                const u32 x = (raw - pn.lo) * 100u;
-                const u32 t = __umulhi(x, pn.mlo);
-                const u32 q = (x * pn.mhi + t) >> 25;
-                if (n < s.n_nodes) {
-                    raw_out[row + n] = (i64)raw;   // filter.go:84-86 is the identity below 2^63
-                    norm_out[row + n] = fit ? (u8)q : (u8)0;
-                }
-                if (lane == 0 && base + j * 32 < stride) bits_out[(size_t)pod.orig * (stride / 32) + ((base + j * 32) >> 5)] = fitmask[j];
+        for (int j = NPL - 1; j >= 0; --j) {
+            if (fitm[j] && rmax[j] == pn.y) {  // warp-uniform: some lane of this slot holds the top score
+                const u32 topmask = __ballot_sync(0xFFFFFFFFu, fitl[j] && (u32)raw64[j] == pn.y);
+                best = base + j * 32 + (__ffs(topmask) - 1);
+            }
+        }
+        if (WRITE) {
+            const size_t row = (size_t)pod.orig * stride;
+#pragma unroll
+            for (int j = 0; j < NPL; ++j) {
+                rawp[row + j * 32] = raw64[j];
+                normp[row + j * 32] = (u8)qn[j];
+            }
+            if (lane == 0) {
+                u32 *bp = bitsp + (size_t)pod.orig * (stride >> 5);
+                if (NPL == 4) *reinterpret_cast<uint4 *>(bp) = make_uint4(fitm[0], fitm[1], fitm[2], fitm[3]);
+                else if (NPL == 2) *reinterpret_cast<uint2 *>(bp) = make_uint2(fitm[0], fitm[1]);
+                else
+#pragma unroll
+                    for (int j = 0; j < NPL; ++j) bp[j] = fitm[j];
             }
         }
         if (lane == 0) {
@@ -620,7 +653,7 @@ __global__ void __launch_bounds__(HOT_THREADS) k_fast_out(DevSnap s, const PodS 
             cnt2 += cnt_s[w][i];
             best = min(best, best_s[w][i]);
         }
-        const u32 orig = sp[i].orig;
+        const u32 orig = sp[2 * i + 1].y;
         if (cnt2) atomicAdd(&count[orig], (u64)cnt2);
         if (best != 0xFFFFFFFFu) atomicMax(&ckey[orig], ckey_of(s.node_base + best));
     }

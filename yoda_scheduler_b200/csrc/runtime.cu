@@ -733,7 +733,7 @@ static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
     if (c->flushed_uncommitted || c->n_upd)
         return fail(YODA_E_STATE, "uncommitted node updates are pending: call yoda_commit before evaluating");
     TRY(ensure_pods(c, P));
-    c->stride = round_up(std::max(c->snap.n_nodes, 1u), 128);
+    c->stride = round_up(std::max(c->snap.n_nodes, 1u), 1024);  // rows padded to the hot kernels' CTA tile
     if (flags & YODA_EVAL_FULL) TRY(ensure_matrices(c, P, c->stride));
     c->ph_path = (c->narrow_ok && !(flags & YODA_EVAL_FORCE_DIRECT)) ? 1 : 0;
     if (c->ph_path == 1) TRY(ensure_fast(c, P));
