@@ -486,32 +486,32 @@ __global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const Pod
     u32 hi_l[NPL], lo_l[NPL], bound[NPL];
 #pragma unroll
     for (int j = 0; j < NPL; ++j) { hi_l[j] = 0; lo_l[j] = 0xFFFFFFFFu; bound[j] = 0; }
-    u32 hi_w = 0, lo_w = 0xFFFFFFFFu;
+    u32 hi_w = 0, lo_w = 0xFFFFFFFFu, bmin = 0;  // bmin = min over the lane's slots of bound[j]
     for (u32 i = 0; i < cn; ++i) {
         const PodRegs pod = pod_from_smem(sp, i);
         const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
-        if (pod.cls != cur_cls) hot_load_class(r, s, tables, pod.cls, base, lane);
-        cur_cls = pod.cls; cur_gid = pod.gid; cur_m = pod.m;
-        bool any_miss = false;
+        if (!same || __any_sync(0xFFFFFFFFu, pod.m > bmin)) {
+            if (pod.cls != cur_cls) hot_load_class(r, s, tables, pod.cls, base, lane);
+            cur_cls = pod.cls; cur_gid = pod.gid;
 #pragma unroll
-        for (int j = 0; j < NPL; ++j) {
-            if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
-                bool fit;
-                u32 b;
-                const u32 raw = hot_eval(r, j, pod.m, pod.c, pod.num, pod.reqM, pod.reqC, fit, b);
-                bound[j] = fit ? b : 0xFFFFFFFFu;
-                hi_l[j] = fit ? raw : 0u;
-                lo_l[j] = fit ? raw : 0xFFFFFFFFu;
-                any_miss = true;
+            for (int j = 0; j < NPL; ++j) {
+                if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
+                    bool fit;
+                    u32 b;
+                    const u32 raw = hot_eval(r, j, pod.m, pod.c, pod.num, pod.reqM, pod.reqC, fit, b);
+                    bound[j] = fit ? b : 0xFFFFFFFFu;
+                    hi_l[j] = fit ? raw : 0u;
+                    lo_l[j] = fit ? raw : 0xFFFFFFFFu;
+                }
             }
-        }
-        if (any_miss) {
             u32 hi = hi_l[0], lo = lo_l[0];
+            bmin = bound[0];
 #pragma unroll
-            for (int j = 1; j < NPL; ++j) { hi = max(hi, hi_l[j]); lo = min(lo, lo_l[j]); }
+            for (int j = 1; j < NPL; ++j) { hi = max(hi, hi_l[j]); lo = min(lo, lo_l[j]); bmin = min(bmin, bound[j]); }
             hi_w = __reduce_max_sync(0xFFFFFFFFu, hi);
             lo_w = __reduce_min_sync(0xFFFFFFFFu, lo);
         }
+        cur_m = pod.m;
         if (lane == 0) {
             hi_s[warp][i] = hi_w;
             lo_s[warp][i] = lo_w;
@@ -578,7 +578,7 @@ __global__ void __launch_bounds__(HOT_THREADS) k_fast_out(DevSnap s, const PodS 
     u32 fitl[NPL], qn[NPL], rmax[NPL];  // lane mask (0 / ~0), normalized score, best feasible score of the slot
 #pragma unroll
     for (int j = 0; j < NPL; ++j) { raw64[j] = 0; bound[j] = 0; fitm[j] = 0; fitl[j] = 0; qn[j] = 0; rmax[j] = 0; }
-    u32 cnt = 0;
+    u32 cnt = 0, bmin = 0, wmax = 0;  // bmin: min bound over the lane's slots; wmax: best feasible score of the warp's nodes
     unsigned long long *rawp = reinterpret_cast<unsigned long long *>(raw_out) + base + lane;
     u8 *normp = norm_out + base + lane;
     u32 *bitsp = bits_out + (base >> 5);
@@ -587,41 +587,49 @@ __global__ void __launch_bounds__(HOT_THREADS) k_fast_out(DevSnap s, const PodS 
         const uint4 pn = sn[i];  // lo, hi, mhi, mlo
         const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
         const bool nsame = same && (pn.x == cur_lo) && (pn.y == cur_hi);
-        if (pod.cls != cur_cls) hot_load_class(r, s, tables, pod.cls, base, lane);
-        cur_cls = pod.cls; cur_gid = pod.gid; cur_m = pod.m; cur_lo = pn.x; cur_hi = pn.y;
-        bool any_miss = false;
+        const bool miss_any = !same || __any_sync(0xFFFFFFFFu, pod.m > bmin);
+        if (miss_any) {
+            if (pod.cls != cur_cls) hot_load_class(r, s, tables, pod.cls, base, lane);
+            cur_cls = pod.cls; cur_gid = pod.gid;
+            cnt = 0; wmax = 0;
 #pragma unroll
-        for (int j = 0; j < NPL; ++j) {
-            const bool miss = !same || __any_sync(0xFFFFFFFFu, pod.m > bound[j]);
-            if (miss) {
-                bool fit;
-                u32 b;
-                const u32 raw = hot_eval(r, j, pod.m, pod.c, pod.num, pod.reqM, pod.reqC, fit, b);
-                bound[j] = fit ? b : 0xFFFFFFFFu;
-                raw64[j] = raw;  // filter.go:84-86 is the identity below 2^63
-                fitm[j] = __ballot_sync(0xFFFFFFFFu, fit);
-                fitl[j] = fit ? 0xFFFFFFFFu : 0u;
-                rmax[j] = __reduce_max_sync(0xFFFFFFFFu, fit ? raw : 0u);
-                any_miss = true;
+            for (int j = 0; j < NPL; ++j) {
+                if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
+                    bool fit;
+                    u32 b;
+                    const u32 raw = hot_eval(r, j, pod.m, pod.c, pod.num, pod.reqM, pod.reqC, fit, b);
+                    bound[j] = fit ? b : 0xFFFFFFFFu;
+                    raw64[j] = raw;  // filter.go:84-86 is the identity below 2^63
+                    fitm[j] = __ballot_sync(0xFFFFFFFFu, fit);
+                    fitl[j] = fit ? 0xFFFFFFFFu : 0u;
+                    rmax[j] = __reduce_max_sync(0xFFFFFFFFu, fit ? raw : 0u);
+                    if (WRITE && nsame) {
+                        const u32 x = ((u32)raw64[j] - pn.x) * 100u;
+                        qn[j] = ((x * pn.z + __umulhi(x, pn.w)) >> 25) & fitl[j];
+                    }
+                }
+                cnt += __popc(fitm[j]);
+                wmax = max(wmax, rmax[j]);
             }
-            if (WRITE && (miss || !nsame)) {
-                // scheduler.go:152: (raw - lo) * 100 / (hi - lo), exact via the 57-bit reciprocal
+            bmin = bound[0];
+#pragma unroll
+            for (int j = 1; j < NPL; ++j) bmin = min(bmin, bound[j]);
+        }
+        if (WRITE && !nsame) {
+            // scheduler.go:152: (raw - lo) * 100 / (hi - lo), exact via the 57-bit reciprocal
+#pragma unroll
+            for (int j = 0; j < NPL; ++j) {
                 const u32 x = ((u32)raw64[j] - pn.x) * 100u;
-                const u32 t = __umulhi(x, pn.w);
-                qn[j] = ((x * pn.z + t) >> 25) & fitl[j];
+                qn[j] = ((x * pn.z + __umulhi(x, pn.w)) >> 25) & fitl[j];
             }
         }
-        if (any_miss) {
-            cnt = 0;
-#pragma unroll
-            for (int j = 0; j < NPL; ++j) cnt += __popc(fitm[j]);
-        }
+        cur_m = pod.m; cur_lo = pn.x; cur_hi = pn.y;
         u32 best = 0xFFFFFFFFu;
+        if (cnt && wmax == pn.y) {  // warp-uniform: some lane of this warp holds the pod's top score
 #pragma unroll
-        for (int j = NPL - 1; j >= 0; --j) {
-            if (fitm[j] && rmax[j] == pn.y) {  // warp-uniform: some lane of this slot holds the top score
+            for (int j = NPL - 1; j >= 0; --j) {
                 const u32 topmask = __ballot_sync(0xFFFFFFFFu, fitl[j] && (u32)raw64[j] == pn.y);
-                best = base + j * 32 + (__ffs(topmask) - 1);
+                if (topmask) best = base + j * 32 + (__ffs(topmask) - 1);
             }
         }
         if (WRITE) {
