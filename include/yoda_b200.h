@@ -150,6 +150,18 @@ int yoda_result_matrices(yoda_ctx *ctx, void **d_bits, void **d_raw, void **d_no
  * used when the framework's list is not Yoda's own feasible set (other plugins filtered too). */
 int yoda_normalize_scores(yoda_ctx *ctx, int64_t *scores, uint32_t n);
 
+/* No counterpart in the reference.  The same rescale for callers that may not allocate: no
+ * context, no cudaMalloc/cudaFree, no host allocation -- the only scratch is a fixed 16 KiB array
+ * inside the library image (resident on every GPU that loads the library, until exit), which
+ * limits the list to YODA_NOALLOC_MAX_SCORES.  d_scores_in / d_scores_out are device pointers on
+ * the current device (they may be equal); the work is queued on cuda_stream (cudaStream_t, NULL =
+ * default stream) and is not waited for.  The first call on each device looks up the scratch
+ * address; make that call before any stream capture begins.  Calls on one device share the
+ * scratch: calls whose kernels overlap on the GPU race, so serialise them.  Longer lists are
+ * rejected with YODA_E_RANGE. */
+#define YODA_NOALLOC_MAX_SCORES (1u << 20)
+int yoda_normalize_scores_noalloc(const int64_t *d_scores_in, int64_t *d_scores_out, uint32_t n, void *cuda_stream);
+
 /* filter.StrToUint64 / strToUint (filter.go:60-74): strconv.Atoi, any error -> 0 */
 uint64_t yoda_parse_label(const char *s, size_t len);
 /* filter.Uint64ToInt64 (filter.go:84-86): values >= 2^63 -> 0 */
@@ -173,7 +185,8 @@ typedef struct {
 } yoda_xchg;
 /* phases: 0 = upload pods + local maxima; 1 = local lowest/highest/count; 2 = local output pass
  * and node choice; 3 = finish (write results).  After phases 0, 1 and 2 the buffers returned by
- * yoda_phase_exchange must be reduced across shards before the next phase runs. */
+ * yoda_phase_exchange must be reduced across shards before the next phase runs
+ * (phase 0: the six maxima; phase 1: highest / ~lowest; phase 2: choice keys (MAX) and feasible counts (SUM)). */
 int yoda_phase_begin(yoda_ctx *ctx, const yoda_pod_req *pods, uint32_t n_pods, uint32_t flags);
 int yoda_phase_run(yoda_ctx *ctx, int phase);
 int yoda_phase_exchange(yoda_ctx *ctx, int phase, yoda_xchg *bufs, int *n_bufs /* in: capacity, out: used */);
