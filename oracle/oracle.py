@@ -43,6 +43,7 @@ def lib():
         L.ora_eval_batch.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 8
         L.ora_filter.argtypes = [C.c_void_p, C.c_uint32, C.c_char_p, C.c_char_p, C.c_char_p]
         L.ora_node_static.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+        L.ora_score_with_max.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -132,6 +133,16 @@ class OracleCluster:
         if rc:
             raise ZeroDivisionError("TotalMemorySum == 0 panics in the reference (algorithm.go:71,86)")
         return a.value, b.value
+
+    def score_with_max(self, labels: dict, max6):
+        """(feasible, raw) of every node for one pod under given collection.MaxValue maxima."""
+        enc = lambda k: None if k not in labels else labels[k].encode()
+        mx = np.ascontiguousarray(max6, dtype=np.uint64)
+        feas = np.zeros(self.n, np.uint8)
+        raw = np.zeros(self.n, np.int64)
+        rc = lib().ora_score_with_max(self._h, enc("scv/number"), enc("scv/memory"), enc("scv/clock"), mx.ctypes.data, feas.ctypes.data, raw.ctypes.data)
+        assert rc == 0, rc
+        return feas, raw
 
     def eval(self, pods: Sequence[dict], faithful: bool = False, threads: int = 1, full: bool = True) -> dict:
         """pods: list of label dicts (keys scv/number, scv/memory, scv/clock; others ignored)."""

@@ -632,3 +632,26 @@ int ora_node_static(const ora_cluster *cl, uint32_t node, uint64_t *alloc, uint6
     if (rc) return rc;
     return calculate_actual_score(&cl->nodes[node], actual);
 }
+
+/* Score of every node of `cl` for one pod under GIVEN maxima (a node shard scoring with the
+ * cluster-wide collection.MaxValue).  raw[n] as in ora_eval_batch; feasible[n] = Filter verdict. */
+int ora_score_with_max(const ora_cluster *cl, const char *number, const char *memory, const char *clock,
+                       const uint64_t *max6, uint8_t *feasible, int64_t *raw) {
+    const char *keys[3], *vals[3];
+    uint32_t k = 0;
+    ora_labels pod = {0, NULL};
+    if (memory) { keys[k] = "scv/memory"; vals[k++] = memory; }
+    if (number) { keys[k] = "scv/number"; vals[k++] = number; }
+    if (clock) { keys[k] = "scv/clock"; vals[k++] = clock; }
+    labels_set(&pod, k, keys, vals);
+    ora_max mx = {max6[0], max6[1], max6[2], max6[3], max6[4], max6[5]};
+    int rc = ORA_OK;
+    for (uint32_t n = 0; n < cl->n_nodes && !rc; ++n) {
+        const ora_node *nd = &cl->nodes[n];
+        feasible[n] = (uint8_t)yoda_filter(&pod, nd);
+        raw[n] = 0;
+        if (nd->has_scv) rc = yoda_score(&mx, &pod, nd, &raw[n]);
+    }
+    labels_free(&pod);
+    return rc;
+}

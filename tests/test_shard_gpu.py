@@ -1,0 +1,102 @@
+"""Node sharding on the GPU: shards driven through the phase API must reproduce the single-context
+result bit for bit (and hence the oracle)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from parity import assert_matches_oracle
+from yoda_scheduler_b200 import api, shard, synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("flags", [api.EVAL_FULL, api.EVAL_FULL | api.EVAL_FORCE_DIRECT, api.EVAL_DECIDE])
+@pytest.mark.parametrize("n_shards", [2, 3])
+def test_shards_on_one_gpu_equal_single(n_shards, flags):
+    """All shards live on cuda:0 and run one after the other; the exchange between phases is an
+    element-wise max / sum over the shards' partial buffers (what NCCL does across GPUs)."""
+    import torch
+    dev = torch.device("cuda", 0)
+    N, P = 3000, 500
+    snap = synth.make_snapshot(N)
+    reqs = synth.make_requests(P, 31)
+    labels = synth.make_pod_labels(P, 31)
+    with api.Context(N) as single:
+        single.load_snapshot(snap)
+        want = single.eval(reqs, flags)
+        want_m = single.fetch_all(P) if flags & api.EVAL_FULL else None
+    bounds = np.linspace(0, N, n_shards + 1).astype(int)
+    ctxs = []
+    for r in range(n_shards):
+        lo, hi = int(bounds[r]), int(bounds[r + 1])
+        c = api.Context(hi - lo, node_base=lo, shard_rank=r, shard_count=n_shards)
+        c.load_snapshot(snap.slice(lo, hi))
+        c.phase_begin(reqs, flags)
+        ctxs.append(c)
+    for phase in (0, 1, 2):
+        for c in ctxs:
+            c.phase_run(phase)
+        bufs = [c.phase_exchange(phase) for c in ctxs]
+        for k in range(len(bufs[0])):
+            ts = [shard.device_tensor(b[k][0], b[k][1], dev) for b in bufs]
+            op = bufs[0][k][2]
+            if op == shard.XCHG_SUM:
+                red = torch.stack(ts).sum(0)
+            else:
+                red = (torch.stack(ts) ^ shard.SIGN).max(0).values ^ shard.SIGN   # unsigned max
+            for t in ts:
+                t.copy_(red)
+        torch.cuda.synchronize()
+    got = []
+    for c in ctxs:
+        c.phase_run(3)
+        got.append(c.phase_finish())
+    for g in got:
+        assert np.array_equal(g, want)          # every shard ends with the same global per-pod results
+    if flags & api.EVAL_FULL:
+        mats = [c.fetch_all(P) for c in ctxs]
+        for k in ("feasible", "raw", "norm"):
+            assert np.array_equal(np.concatenate([m[k] for m in mats], axis=1), want_m[k]), k
+        assert_matches_oracle(snap, labels, want, want_m)
+    for c in ctxs:
+        c.close()
+
+
+def _nccl_worker(rank, world, port, N, P, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from yoda_scheduler_b200 import api, shard, synth
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world, device_id=dev)
+    per = N // world
+    ctx = api.Context(per, device=rank, node_base=rank * per, shard_rank=rank, shard_count=world)
+    shard.init_nccl(ctx, rank, world, dev)
+    ctx.load_snapshot(synth.make_snapshot(per, node_offset=rank * per))
+    reqs = synth.make_requests(P, 31)
+    res = ctx.eval(reqs, api.EVAL_FULL)                       # exchanges run inside the library (NCCL)
+    res2 = shard.eval_host_driven(ctx, reqs, api.EVAL_FULL, dev)   # same through torch.distributed
+    assert np.array_equal(res, res2)
+    np.save(os.path.join(out_dir, f"res{rank}.npy"), res)
+    dist.barrier()
+    ctx.close()
+    dist.destroy_process_group()
+
+
+def test_two_gpus_nccl(tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    N, P, world = 4000, 600, 2
+    port = 29500 + os.getpid() % 2000
+    mp.spawn(_nccl_worker, args=(world, port, N, P, str(tmp_path)), nprocs=world, join=True)
+    with api.Context(N) as single:
+        single.load_snapshot(synth.make_snapshot(N))
+        want = single.eval(synth.make_requests(P, 31), api.EVAL_FULL)
+    for r in range(world):
+        assert np.array_equal(np.load(tmp_path / f"res{r}.npy"), want)
