@@ -38,6 +38,18 @@ def algorithmic_bytes(P, N):
     return N * R_NODE + P * R_POD + P * R_OUT + P * N * W_BYTES
 
 
+def profiled_traffic(config, mode, path):
+    """dram bytes of the output pass per step from the committed ncu --set full capture (same workload)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        if t["config"] == f"{config} {mode}" and path == 1:
+            return float(t["dram_bytes_read"]) + float(t["dram_bytes_write"])
+    except Exception:
+        pass
+    return None
+
+
 def measured_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -144,7 +156,7 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c3", choices=["c1", "c2", "c3", "c4", "c5"])
@@ -153,6 +165,7 @@ def main():
     ap.add_argument("--mode", default="full", choices=["full", "decide"])
     ap.add_argument("--force-direct", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-latency", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
@@ -275,12 +288,28 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "output pass (write_ms)", "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None,
+                         "frac": achieved / peak, "traffic": profiled_traffic(args.config, args.mode, t_last.path), "algorithmic_bytes": kern_bytes,
                          "step_achieved": step_bytes / (phase["total"] / steps * 1e-3) / 1e9 if phase["total"] > 0 else 0.0,
                          "step_frac": step_bytes / (phase["total"] / steps * 1e-3) / 1e9 / peak if phase["total"] > 0 else 0.0,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
             "phases_ms": {k: v / steps for k, v in phase.items()},
         }
+        if world == 1 and not args.no_latency:
+            # p50/p99 batch latency at this snapshot size, host buffers in -> per-pod results out
+            lat = {}
+            for pp, reps in ((1, 300), (1000, 300), (n_pods, 40)):
+                if pp > n_pods:
+                    continue
+                sub = np.ascontiguousarray(reqs_np[:pp])
+                outb = np.zeros(pp, api.POD_RES)
+                ts = []
+                for i in range(reps + 20):
+                    t0 = time.perf_counter()
+                    api.check(ctx.L.yoda_eval_batch(ctx.h, sub.ctypes.data, pp, flags, outb.ctypes.data))
+                    if i >= 20:
+                        ts.append((time.perf_counter() - t0) * 1e3)
+                lat[f"pods={pp}"] = {"p50_ms": float(np.percentile(ts, 50)), "p99_ms": float(np.percentile(ts, 99)), "batches": reps}
+            line["latency"] = {"nodes": n_nodes, "mode": args.mode, **lat}
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             all_labels = synth.make_pod_labels(min(n_pods, 4096), pod_seed)
