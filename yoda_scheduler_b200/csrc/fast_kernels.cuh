@@ -238,53 +238,40 @@ __global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupD
     }
 }
 
-// one CTA per group: suffix maximum over the group's pod segment, result max(1, .) into max6[orig]
-#define SCANT 256
+// one CTA per (group, field): suffix maximum over the group's pod segment, result max(1, .) into max6[orig]
+#define SCANT 1024
 __global__ void __launch_bounds__(SCANT) k_max_scan(const GroupDesc *__restrict__ gdesc, u32 n_groups, const u32 *__restrict__ step,
                                                     const PodS *__restrict__ pods, u64 *max6, u32 P) {
-    const u32 gid = blockIdx.x;
+    const u32 gid = blockIdx.x, f = blockIdx.y;
     if (gid >= n_groups) return;
     const GroupDesc gd = gdesc[gid];
-    __shared__ u32 warp_max[6][SCANT / 32];
-    __shared__ u32 carry_s[6];
+    __shared__ u32 warp_max[SCANT / 32];
+    __shared__ u32 carry_s;
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x < 6) carry_s[threadIdx.x] = 0;
+    if (threadIdx.x == 0) carry_s = 0;
     __syncthreads();
-    // walk the segment backwards in tiles of SCANT; thread t handles position end-1-t of the tile
+    const u32 *sf = step + (size_t)f * P;
+    // walk the segment backwards in tiles of SCANT; thread t handles position top-1-t of the tile
     for (u32 top = gd.seg_end; top > gd.seg_start;) {
         const u32 cnt = min(SCANT, top - gd.seg_start);
         const bool live = threadIdx.x < cnt;
         const u32 pos = live ? top - 1 - threadIdx.x : 0;
-        u32 v[6];
-#pragma unroll
-        for (int f = 0; f < 6; ++f) v[f] = live ? step[(size_t)f * P + pos] : 0u;
+        u32 v = live ? sf[pos] : 0u;
         // inclusive prefix max over threadIdx (= suffix max over positions)
 #pragma unroll
-        for (int f = 0; f < 6; ++f) {
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const u32 t = __shfl_up_sync(0xFFFFFFFFu, v[f], o);
-                if (lane >= (u32)o) v[f] = max(v[f], t);
-            }
-            if (lane == 31) warp_max[f][warp] = v[f];
+        for (int o = 1; o < 32; o <<= 1) {
+            const u32 t = __shfl_up_sync(0xFFFFFFFFu, v, o);
+            if (lane >= (u32)o) v = max(v, t);
         }
+        if (lane == 31) warp_max[warp] = v;
         __syncthreads();
-#pragma unroll
-        for (int f = 0; f < 6; ++f) {
-            u32 pre = carry_s[f];
-            for (u32 w = 0; w < warp; ++w) pre = max(pre, warp_max[f][w]);
-            v[f] = max(v[f], pre);
-        }
-        if (live) {
-            const u32 orig = pods[pos].orig;
-#pragma unroll
-            for (int f = 0; f < 6; ++f) max6[(size_t)orig * 6 + f] = (u64)max(v[f], 1u);  // collection.go:31-38
-        }
+        u32 pre = carry_s;
+        for (u32 w = lane; w < warp; w += 32) pre = max(pre, warp_max[w]);
+        pre = __reduce_max_sync(0xFFFFFFFFu, pre);
+        v = max(v, pre);
+        if (live) max6[(size_t)pods[pos].orig * 6 + f] = (u64)max(v, 1u);  // collection.go:31-38
         __syncthreads();
-        if (threadIdx.x == SCANT - 1) {
-#pragma unroll
-            for (int f = 0; f < 6; ++f) carry_s[f] = v[f];
-        }
+        if (threadIdx.x == SCANT - 1) carry_s = v;
         __syncthreads();
         top -= cnt;
     }

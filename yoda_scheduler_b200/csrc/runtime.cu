@@ -606,7 +606,7 @@ static int fast_phase0(yoda_ctx *c) {
         k_max_thresholds<<<grid, MAXT, 0, st>>>(c->snap, c->fw_gdesc, c->fw_n_groups, c->fw_m_sorted, c->fw_step, P);
         LAUNCHED(c);
     }
-    k_max_scan<<<c->fw_n_groups, SCANT, 0, st>>>(c->fw_gdesc, c->fw_n_groups, c->fw_step, c->fw_pods, c->d_max6, P);
+    k_max_scan<<<dim3(c->fw_n_groups, 6), SCANT, 0, st>>>(c->fw_gdesc, c->fw_n_groups, c->fw_step, c->fw_pods, c->d_max6, P);
     LAUNCHED(c);
     return YODA_OK;
 }
@@ -614,7 +614,7 @@ static int fast_phase0(yoda_ctx *c) {
 template <bool CLK>
 static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
-    constexpr int NPL = CLK ? 2 : 4;
+    constexpr int NPL = 4;
     dim3 grid((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (p_end - p_begin + HOT_CHUNK - 1) / HOT_CHUNK);
     k_fast_score<NPL, CLK><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo);
     LAUNCHED(c);
@@ -624,7 +624,7 @@ static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
 template <bool CLK>
 static int fast_out_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
-    constexpr int NPL = CLK ? 2 : 4;
+    constexpr int NPL = 4;
     dim3 grid((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (p_end - p_begin + HOT_CHUNK - 1) / HOT_CHUNK);
     if (c->ph_flags & YODA_EVAL_FULL)
         k_fast_out<NPL, CLK, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->fw_nrm, p_begin, p_end, c->fw_tables,
