@@ -33,3 +33,18 @@ def build(force: bool = False, verbose: bool = False) -> str:
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + cus + ["-ldl"]
     subprocess.check_call(cmd, cwd=CSRC)
     return SO
+
+
+HOST = os.path.join(HERE, "host")
+HARNESS = os.path.join(HOST, "yoda_harness")
+
+
+def build_host(force: bool = False) -> str:
+    """C++ host layer: plugin mirror + fake-framework benchmark harness (links libyoda_b200.so)."""
+    srcs = [os.path.join(HOST, f) for f in ("harness.cpp", "yoda_plugin.cpp")]
+    deps = [os.path.join(HOST, f) for f in os.listdir(HOST) if f.endswith((".cpp", ".hpp"))] + [SO]
+    if not force and os.path.exists(HARNESS) and all(os.path.getmtime(d) <= os.path.getmtime(HARNESS) for d in deps):
+        return HARNESS
+    cmd = [os.environ.get("CXX", "g++"), "-std=c++17", "-O2", "-Wall", "-o", HARNESS] + srcs + ["-L" + HERE, "-lyoda_b200", "-Wl,-rpath,$ORIGIN/..", "-lpthread"]
+    subprocess.check_call(cmd, cwd=HOST)
+    return HARNESS
