@@ -1,0 +1,159 @@
+// Package b200 is the thin cgo shim over include/yoda_b200.h.  No Go pointer is retained by C:
+// every buffer is passed for the duration of one call only.
+package b200
+
+/*
+#cgo CFLAGS: -I${SRCDIR}/../../../../include
+#cgo LDFLAGS: -L${SRCDIR}/../../../../yoda_scheduler_b200 -lyoda_b200
+#include <stdlib.h>
+#include "yoda_b200.h"
+*/
+import "C"
+
+import (
+	"fmt"
+	"unsafe"
+)
+
+const (
+	MaxCards    = C.YODA_MAX_CARDS
+	HasNumber   = C.YODA_POD_HAS_NUMBER
+	HasMemory   = C.YODA_POD_HAS_MEMORY
+	HasClock    = C.YODA_POD_HAS_CLOCK
+	RowFeasible = C.YODA_ROW_FEASIBLE_BITS
+	RowRaw      = C.YODA_ROW_RAW
+	RowNorm     = C.YODA_ROW_NORM
+)
+
+type (
+	NodeRecord = C.yoda_node_record
+	PodReq     = C.yoda_pod_req
+	PodResult  = C.yoda_pod_result
+)
+
+type Ctx struct{ h *C.yoda_ctx }
+
+func lastErr(rc C.int) error {
+	return fmt.Errorf("yoda_b200 error %d: %s", int(rc), C.GoString(C.yoda_last_error()))
+}
+
+func New(device int, maxNodes uint32) (*Ctx, error) {
+	cfg := C.yoda_config{device: C.int32_t(device), max_nodes: C.uint32_t(maxNodes), shard_count: 1}
+	var h *C.yoda_ctx
+	if rc := C.yoda_create(&cfg, &h); rc != 0 {
+		return nil, lastErr(rc)
+	}
+	return &Ctx{h}, nil
+}
+
+func (c *Ctx) Close() { C.yoda_destroy(c.h); c.h = nil }
+
+func (c *Ctx) Upsert(idx uint32, rec *NodeRecord) error {
+	if rc := C.yoda_node_upsert(c.h, C.uint32_t(idx), rec); rc != 0 {
+		return lastErr(rc)
+	}
+	return nil
+}
+
+func (c *Ctx) SetAlloc(idx uint32, sum uint64) error {
+	if rc := C.yoda_node_set_alloc(c.h, C.uint32_t(idx), C.uint64_t(sum)); rc != 0 {
+		return lastErr(rc)
+	}
+	return nil
+}
+
+func (c *Ctx) Remove(idx uint32) error {
+	if rc := C.yoda_node_remove(c.h, C.uint32_t(idx)); rc != 0 {
+		return lastErr(rc)
+	}
+	return nil
+}
+
+func (c *Ctx) Commit() (uint64, error) {
+	var e C.uint64_t
+	if rc := C.yoda_commit(c.h, &e); rc != 0 {
+		return 0, lastErr(rc)
+	}
+	return uint64(e), nil
+}
+
+func (c *Ctx) NodeCount() uint32 {
+	var n C.uint32_t
+	C.yoda_node_count(c.h, &n)
+	return uint32(n)
+}
+
+// Eval: Filter + CollectMaxValues + Score + NormalizeScore + node choice for all pods in one pass.
+func (c *Ctx) Eval(pods []PodReq, full bool) ([]PodResult, error) {
+	out := make([]PodResult, len(pods))
+	if len(pods) == 0 {
+		return out, nil
+	}
+	flags := C.uint32_t(C.YODA_EVAL_DECIDE)
+	if full {
+		flags = C.uint32_t(C.YODA_EVAL_FULL)
+	}
+	rc := C.yoda_eval_batch(c.h, (*C.yoda_pod_req)(unsafe.Pointer(&pods[0])), C.uint32_t(len(pods)), flags,
+		(*C.yoda_pod_result)(unsafe.Pointer(&out[0])))
+	if rc != 0 {
+		return nil, lastErr(rc)
+	}
+	return out, nil
+}
+
+func (c *Ctx) Row(pod uint32, kind int, dst unsafe.Pointer, bytes int) error {
+	if rc := C.yoda_fetch_row(c.h, C.uint32_t(pod), C.int(kind), dst, C.size_t(bytes)); rc != 0 {
+		return lastErr(rc)
+	}
+	return nil
+}
+
+// NormalizeScores: scheduler.go:132-157 on an arbitrary list, in place, on the device.
+func (c *Ctx) NormalizeScores(scores []int64) error {
+	if rc := C.yoda_normalize_scores(c.h, (*C.int64_t)(unsafe.Pointer(&scores[0])), C.uint32_t(len(scores))); rc != 0 {
+		return lastErr(rc)
+	}
+	return nil
+}
+
+// U64 converts to the C field type of yoda_pod_req.
+func U64(v uint64) C.uint64_t { return C.uint64_t(v) }
+
+// MakeRecord / MakeReq / Chosen: helpers for callers outside this package (cgo field names are
+// not exported across packages).
+func MakeRecord(cardNumber uint64, healthy uint32, free, total []uint64, clock, core, bandwidth, power uint64) *NodeRecord {
+	var r NodeRecord
+	r.card_number = C.uint64_t(cardNumber)
+	r.n_cards = C.uint32_t(len(free))
+	r.healthy_mask = C.uint32_t(healthy)
+	var fs, ts uint64
+	for g := range free {
+		r.free_memory[g], r.total_memory[g] = C.uint64_t(free[g]), C.uint64_t(total[g])
+		r.clock[g], r.core[g], r.bandwidth[g], r.power[g] = C.uint64_t(clock), C.uint64_t(core), C.uint64_t(bandwidth), C.uint64_t(power)
+		fs, ts = fs+free[g], ts+total[g]
+	}
+	if ts == 0 {
+		ts = 1
+	}
+	r.free_memory_sum, r.total_memory_sum = C.uint64_t(fs), C.uint64_t(ts)
+	return &r
+}
+
+func MakeReq(hasNum, hasMem, hasClk bool, num, mem, clk uint64) PodReq {
+	var r PodReq
+	if hasNum {
+		r.flags |= HasNumber
+		r.number = C.uint64_t(num)
+	}
+	if hasMem {
+		r.flags |= HasMemory
+		r.memory = C.uint64_t(mem)
+	}
+	if hasClk {
+		r.flags |= HasClock
+		r.clock = C.uint64_t(clk)
+	}
+	return r
+}
+
+func Chosen(r *PodResult) int32 { return int32(r.chosen) }
