@@ -116,8 +116,6 @@ func (c *Ctx) NormalizeScores(scores []int64) error {
 	return nil
 }
 
-// U64 converts to the C field type of yoda_pod_req.
-func U64(v uint64) C.uint64_t { return C.uint64_t(v) }
 
 // MakeRecord / MakeReq / Chosen: helpers for callers outside this package (cgo field names are
 // not exported across packages).
@@ -156,4 +154,8 @@ func MakeReq(hasNum, hasMem, hasClk bool, num, mem, clk uint64) PodReq {
 	return r
 }
 
-func Chosen(r *PodResult) int32 { return int32(r.chosen) }
+func Chosen(r *PodResult) int32    { return int32(r.chosen) }
+func Feasible(r *PodResult) uint32 { return uint32(r.feasible) }
+func Maxima(r *PodResult) [6]uint64 {
+	return [6]uint64{uint64(r.max_bandwidth), uint64(r.max_clock), uint64(r.max_core), uint64(r.max_free_memory), uint64(r.max_power), uint64(r.max_total_memory)}
+}

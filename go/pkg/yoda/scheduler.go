@@ -75,21 +75,11 @@ func atoiOrZero(s string) uint64 {
 }
 
 func requirement(pod *v1.Pod) b200.PodReq {
-	var r b200.PodReq
 	l := pod.GetLabels()
-	if s, ok := l["scv/number"]; ok {
-		r.flags |= b200.HasNumber
-		r.number = b200.U64(atoiOrZero(s))
-	}
-	if s, ok := l["scv/memory"]; ok {
-		r.flags |= b200.HasMemory
-		r.memory = b200.U64(atoiOrZero(s))
-	}
-	if s, ok := l["scv/clock"]; ok {
-		r.flags |= b200.HasClock
-		r.clock = b200.U64(atoiOrZero(s))
-	}
-	return r
+	num, hasNum := l["scv/number"]
+	mem, hasMem := l["scv/memory"]
+	clk, hasClk := l["scv/clock"]
+	return b200.MakeReq(hasNum, hasMem, hasClk, atoiOrZero(num), atoiOrZero(mem), atoiOrZero(clk))
 }
 
 func New(_ runtime.Object, h framework.Handle) (framework.Plugin, error) {
@@ -243,9 +233,10 @@ func (y *Yoda) PostFilter(_ context.Context, state *framework.CycleState, pod *v
 	if err != nil {
 		return &framework.PostFilterResult{}, framework.NewStatus(framework.Error, err.Error())
 	}
+	mx := b200.Maxima(&m.res) // order of collection.MaxValue: bandwidth, clock, core, free, power, total
 	data := collection.Data{Value: collection.MaxValue{
-		MaxBandwidth: uint(m.res.max_bandwidth), MaxClock: uint(m.res.max_clock), MaxCore: uint(m.res.max_core),
-		MaxFreeMemory: uint64(m.res.max_free_memory), MaxPower: uint(m.res.max_power), MaxTotalMemory: uint64(m.res.max_total_memory),
+		MaxBandwidth: uint(mx[0]), MaxClock: uint(mx[1]), MaxCore: uint(mx[2]),
+		MaxFreeMemory: mx[3], MaxPower: uint(mx[4]), MaxTotalMemory: mx[5],
 	}}
 	state.Lock()
 	state.Write("Max", &data)
@@ -281,7 +272,7 @@ func (y *Yoda) NormalizeScore(_ context.Context, state *framework.CycleState, _ 
 	if d, err := state.Read(memoKey); err == nil {
 		m = d.(*memo)
 	}
-	own := m != nil && uint32(len(scores)) == uint32(m.res.feasible)
+	own := m != nil && uint32(len(scores)) == b200.Feasible(&m.res)
 	for k := 0; own && k < len(scores); k++ {
 		i, ok := y.index[scores[k].Name]
 		own = ok && m.feasible(i) && m.raw[i] == scores[k].Score
