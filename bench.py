@@ -218,10 +218,48 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    # config 5 (metric churn): every step first applies one tick -- 10% of the nodes get new per-card
+    # FreeMemory / health / FreeMemorySum through the pinned update ring -- then schedules the batch
+    churn = args.config == "c5"
+    tick_ms = [0.0, 0]
+    if churn:
+        n_touch = max(1, n_nodes // 10)
+        ticks = []
+        card = np.arange(8, dtype=np.uint64)[None, :]
+        for k in range(8):
+            idx = np.sort(np.random.default_rng(k).choice(n_nodes, n_touch, replace=False)).astype(np.uint32)
+            idx = idx[snap.has_scv[idx] == 1]
+            gidx = (idx.astype(np.uint64) + np.uint64(node_base))[:, None]
+            live = card < snap.n_cards[idx].astype(np.uint64)[:, None]
+            total = snap.total_memory[idx]
+            r = synth.rnd(synth.SEED + 1000 + k, synth.S_FREE, gidx, card) >> np.uint64(32)
+            free = np.where(live, (total * r) >> np.uint64(32), np.uint64(0))      # new FreeMemory, <= TotalMemory
+            healthy = (synth.rnd(synth.SEED + 1000 + k, synth.S_HEALTH, gidx, card) % np.uint64(64) != 0) & live
+            recs = snap.records(idx)
+            recs["free_memory"] = free
+            recs["healthy_mask"] = (healthy.astype(np.uint64) << card).sum(axis=1).astype(np.uint32)
+            recs["free_memory_sum"] = free.sum(axis=1, dtype=np.uint64)
+            ticks.append((idx, recs))
+        tick_no = [0]
+
+        def tick():
+            t0 = time.perf_counter()
+            idx, recs = ticks[tick_no[0] % len(ticks)]
+            tick_no[0] += 1
+            ctx.upsert_many(idx, recs)
+            ctx.commit()
+            tick_ms[0] += (time.perf_counter() - t0) * 1e3
+            tick_ms[1] += 1
+    else:
+        def tick():
+            pass
+
     def step_device():
+        tick()
         ctx.eval_device(d_reqs.data_ptr(), n_pods, flags)
 
     def step_e2e():
+        tick()
         api.check(ctx.L.yoda_eval_batch(ctx.h, h_view.ctypes.data, n_pods, flags, h_out.data_ptr()))
 
     for _ in range(args.warmup):
@@ -294,6 +332,9 @@ def main():
                          "frac_of_nominal_8TBs": achieved / 8000.0},
             "phases_ms": {k: v / steps for k, v in phase.items()},
         }
+        if churn:
+            line["churn"] = {"nodes_updated_per_tick": int(n_touch), "upsert_commit_ms_per_tick": tick_ms[0] / max(tick_ms[1], 1),
+                             "bytes_per_tick": int(n_touch * 432), "note": "tick (pinned ring -> async H2D -> scatter + derive kernels -> epoch) is inside every timed step"}
         if world == 1 and not args.no_latency:
             # p50/p99 batch latency at this snapshot size, host buffers in -> per-pod results out
             lat = {}
