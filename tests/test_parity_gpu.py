@@ -206,3 +206,83 @@ def test_staging_ring_overflow_is_safe():
     labels = synth.make_pod_labels(64, 9)
     res, mats, _ = gpu_cycle(snap, reqs)
     assert_matches_oracle(snap, labels, res, mats)
+
+
+def test_config_c3_full_size_properties():
+    """BASELINE config 3 at full size (50k nodes x 100k pods, 45.6 GB of matrices).  Too big for the oracle
+    in a test, so: (1) the fast path must equal the exact-u64 direct kernels on a random 1500-pod subset,
+    rows included; (2) size-independent invariants over the whole batch; (3) a second run is identical."""
+    n, p, seed = synth.CONFIGS["c3"]
+    snap = synth.make_snapshot(n)
+    reqs = synth.make_requests(p, seed)
+    rng = np.random.default_rng(3)
+    pick = np.sort(rng.choice(p, 1500, replace=False))
+    with api.Context(n) as ctx:
+        ctx.load_snapshot(snap)
+        res = ctx.eval(reqs, api.EVAL_FULL)
+        assert ctx.timing().path == 1
+        rows = {int(i): (ctx.fetch_row(int(i), api.ROW_FEASIBLE_BITS), ctx.fetch_row(int(i), api.ROW_RAW), ctx.fetch_row(int(i), api.ROW_NORM)) for i in pick}
+        again = ctx.eval(reqs, api.EVAL_FULL)
+        assert np.array_equal(res, again)                                   # idempotent
+        sub = ctx.eval(reqs[pick], api.EVAL_FULL | api.EVAL_FORCE_DIRECT)  # exact path, same pods
+        assert ctx.timing().path == 0
+        assert np.array_equal(sub, res[pick])
+        for k, i in enumerate(pick):
+            bits, raw, norm = rows[int(i)]
+            assert np.array_equal(bits, ctx.fetch_row(k, api.ROW_FEASIBLE_BITS))
+            assert np.array_equal(raw, ctx.fetch_row(k, api.ROW_RAW))
+            assert np.array_equal(norm, ctx.fetch_row(k, api.ROW_NORM))
+            r = res[i]
+            assert bits.sum() == r["feasible"]                                # count == popcount of the bit row
+            if r["feasible"]:
+                f = bits.astype(bool)
+                assert raw[f].max() == r["highest"] and norm[f].max() == 100 and norm[~f].max(initial=0) == 0
+                assert r["chosen"] == np.nonzero(f & (raw == r["highest"]))[0][0]   # lowest index holding the top score
+                assert norm[r["chosen"]] == 100
+                lo = r["lowest"]
+                want = (raw[f] - lo) * 100 // (r["highest"] - lo)            # scheduler.go:152 (all terms >= 0 here)
+                assert np.array_equal(norm[f], want.astype(np.uint8))
+            else:
+                assert r["chosen"] == -1 and norm.max() == 0
+    has = res["feasible"] > 0
+    assert (res["chosen"][~has] == -1).all() and (res["chosen"][has] >= 0).all()
+    assert (res["highest"] >= res["lowest"]).all()
+
+
+def test_config_c4_shape_sharded_on_one_gpu():
+    """BASELINE config 4 shape: 1M nodes, node-sharded.  Four 250k-node shards (run one after the other on
+    this GPU, exchanging partials through the phase API) must equal one 1M-node context and the oracle."""
+    import torch
+    from yoda_scheduler_b200 import shard
+    dev = torch.device("cuda", 0)
+    N, P, S = 1_000_000, 384, 4
+    snap = synth.make_snapshot(N)
+    reqs = synth.make_requests(P, synth.CONFIGS["c4"][2])
+    labels = synth.make_pod_labels(P, synth.CONFIGS["c4"][2])
+    with api.Context(N) as single:
+        single.load_snapshot(snap)
+        want = single.eval(reqs, api.EVAL_DECIDE)
+    o = ora.OracleCluster.from_snapshot(snap).eval(labels[:96], threads=16, full=False)
+    assert np.array_equal(want["chosen"][:96], o["chosen"]) and np.array_equal(want["highest"][:96], o["highest"])
+    assert np.array_equal(want["feasible"][:96], o["count"]) and np.array_equal(want["lowest"][:96], o["lowest"])
+    per = N // S
+    ctxs = []
+    for r in range(S):
+        c = api.Context(per, node_base=r * per, shard_rank=r, shard_count=S)
+        c.load_snapshot(snap.slice(r * per, (r + 1) * per))
+        c.phase_begin(reqs, api.EVAL_DECIDE)
+        ctxs.append(c)
+    for phase in (0, 1, 2):
+        for c in ctxs:
+            c.phase_run(phase)
+        bufs = [c.phase_exchange(phase) for c in ctxs]
+        for k in range(len(bufs[0])):
+            ts = [shard.device_tensor(b[k][0], b[k][1], dev) for b in bufs]
+            red = torch.stack(ts).sum(0) if bufs[0][k][2] == shard.XCHG_SUM else (torch.stack(ts) ^ shard.SIGN).max(0).values ^ shard.SIGN
+            for t in ts:
+                t.copy_(red)
+        torch.cuda.synchronize()
+    for c in ctxs:
+        c.phase_run(3)
+        assert np.array_equal(c.phase_finish(), want)
+        c.close()
