@@ -370,14 +370,14 @@ __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__r
 #define HOT_WARPS (HOT_THREADS / 32)
 #define HOT_CHUNK 128  // pods per CTA
 
-template <int NPL, bool CLK>
+template <int NPL>
 struct NodeRegs {
-    u32 fr[NPL][G];
-    u32 cs[NPL][G];
-    u32 ck[CLK ? NPL : 1][G];
+    u32 fr[NPL][G];   // FreeMemory of the node's card slots
+    u32 cs[NPL][G];   // card contributions for the current (group, class): score bits | health bit << 24
     u32 cardnum[NPL];
     u32 stat[NPL];
-    bool ok[NPL];
+    bool ok[NPL];     // node exists and has an SCV
+    bool clkok[NPL];  // enough healthy cards with Clock == c for the current group (true without scv/clock)
 };
 
 __device__ __forceinline__ void load8(const u32 *p, u32 *dst) {
@@ -385,57 +385,69 @@ __device__ __forceinline__ void load8(const u32 *p, u32 *dst) {
     dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; dst[3] = a.w; dst[4] = b.x; dst[5] = b.y; dst[6] = b.z; dst[7] = b.w;
 }
 
-template <int NPL, bool CLK>
-__device__ __forceinline__ void hot_load_nodes(NodeRegs<NPL, CLK> &r, const DevSnap &s, u32 base, u32 lane) {
+template <int NPL>
+__device__ __forceinline__ void hot_load_nodes(NodeRegs<NPL> &r, const DevSnap &s, u32 base, u32 lane) {
 #pragma unroll
     for (int j = 0; j < NPL; ++j) {
         const u32 n = base + j * 32 + lane;
         const bool in = n < s.n_nodes;
         const u32 nn = in ? n : 0;
         load8(s.n32[F_FREE] + (size_t)nn * G, r.fr[j]);
-        if (CLK) load8(s.n32[F_CLOCK] + (size_t)nn * G, r.ck[j]);
         r.cardnum[j] = s.cardnum32[nn];
         r.stat[j] = in ? s.stat32[nn] : 0u;
         r.ok[j] = in && (s.meta[nn] & META_HAS_SCV);
+        r.clkok[j] = true;
     }
 }
-template <int NPL, bool CLK>
-__device__ __forceinline__ void hot_load_class(NodeRegs<NPL, CLK> &r, const DevSnap &s, const u32 *tables, u32 cls, u32 base, u32 lane) {
+
+// (Re)load the per-card contributions when the class or the requirement group changes.  For a
+// group with scv/clock the clock tests are folded in here, once per group instead of once per pod:
+//   - Filter's clock count (healthy cards with Clock == c, filter.go:56-58) becomes the flag clkok;
+//   - cards with Clock < c lose their score bits (collection.go:46 / algorithm.go:48 need
+//     Clock >= c) but keep the health bit, because Filter's memory count ignores the clock.
+template <int NPL>
+__device__ __forceinline__ void hot_load_class(NodeRegs<NPL> &r, const DevSnap &s, const u32 *tables, u32 cls, bool has_clock, u32 c,
+                                               u32 reqC, u32 base, u32 lane) {
 #pragma unroll
     for (int j = 0; j < NPL; ++j) {
         const u32 n = base + j * 32 + lane;
         const u32 nn = n < s.n_nodes ? n : 0;
         load8(tables + ((size_t)cls * s.cap + nn) * G, r.cs[j]);
+        r.clkok[j] = true;
+        if (has_clock) {  // warp-uniform
+            u32 cnt = 0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {  // four cards at a time keeps the transient registers low
+                const uint4 k4 = reinterpret_cast<const uint4 *>(s.n32[F_CLOCK] + (size_t)nn * G)[h];
+                const u32 ck[4] = {k4.x, k4.y, k4.z, k4.w};
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    cnt += (ck[g] == c) ? (r.cs[j][4 * h + g] >> CS_HEALTH_SHIFT) : 0u;
+                    if (ck[g] < c) r.cs[j][4 * h + g] &= ~CS_SCORE_MASK;
+                }
+            }
+            r.clkok[j] = cnt >= reqC;
+        }
     }
 }
 
 // Filter verdict and Score of (pod, node j): `fit`, raw = basic (if fit) + static part, and
 // `bound` = the smallest FreeMemory of the node that is >= m.  For any m' in [m, bound] the set of
 // cards with FreeMemory >= m' is the same, hence so are fit and raw (same group and class).
-template <int NPL, bool CLK>
-__device__ __forceinline__ u32 hot_eval(const NodeRegs<NPL, CLK> &r, int j, u32 m, u32 c, u32 num, u32 reqM, u32 reqC, bool &fit,
-                                        u32 &bound) {
-    u32 acc = 0, cntc = 0, b = 0xFFFFFFFFu;
+template <int NPL>
+__device__ __forceinline__ u32 hot_eval(const NodeRegs<NPL> &r, int j, u32 m, u32 num, u32 reqM, bool &fit, u32 &bound) {
+    u32 acc = 0, b = 0xFFFFFFFFu;
 #pragma unroll
     for (int g = 0; g < G; ++g) {
         const bool q = r.fr[j][g] >= m;  // filter.go:53 / collection.go:46 / algorithm.go:48
         b = q ? min(b, r.fr[j][g]) : b;
-        if (CLK) {
-            cntc += (r.ck[j][g] == c) ? (r.cs[j][g] >> CS_HEALTH_SHIFT) : 0u;  // filter.go:57
-            // Filter counts healthy cards on memory alone; the score sum also needs clock >= c.
-            // Keep the health bit on the memory test and the score bits on both.
-            const u32 add = (r.ck[j][g] >= c) ? r.cs[j][g] : (r.cs[j][g] & ~CS_SCORE_MASK);
-            acc += q ? add : 0u;
-        } else {
-            acc += q ? r.cs[j][g] : 0u;
-        }
+        acc += q ? r.cs[j][g] : 0u;
     }
     bound = b;
-    const u32 cnt = acc >> CS_HEALTH_SHIFT;
-    const u32 basic = acc & CS_SCORE_MASK;
-    fit = r.ok[j] && (num <= r.cardnum[j]) && (cnt >= reqM);
-    if (CLK) fit = fit && (cntc >= reqC);
-    return r.stat[j] + (fit ? basic : 0u);  // algorithm.go:38 (no uint64 wrap in the narrow range)
+    const u32 cnt = acc >> CS_HEALTH_SHIFT;   // healthy cards with FreeMemory >= m (filter.go:52-54)
+    const u32 basic = acc & CS_SCORE_MASK;    // algorithm.go:41-55
+    fit = r.ok[j] && r.clkok[j] && (num <= r.cardnum[j]) && (cnt >= reqM);
+    return r.stat[j] + (fit ? basic : 0u);    // algorithm.go:38 (no uint64 wrap in the narrow range)
 }
 
 // The pods arrive sorted by (group, memory).  Along that order the verdict and score of a node
@@ -446,62 +458,99 @@ __device__ __forceinline__ u32 hot_eval(const NodeRegs<NPL, CLK> &r, int j, u32 
 
 struct PodRegs {
     u32 m, c, num, reqM, reqC, cls, orig, gid;
+    bool has_clock;
 };
 __device__ __forceinline__ PodRegs pod_from_smem(const uint4 *sp, u32 i) {
     const uint4 a = sp[2 * i], b = sp[2 * i + 1];  // PodS: m c num req | cls orig gid pad
     PodRegs p;
     p.m = a.x; p.c = a.y; p.num = a.z; p.reqM = a.w & 0xFFu; p.reqC = (a.w >> 8) & 0xFFu;
+    p.has_clock = (a.w >> 16) & YODA_POD_HAS_CLOCK;
     p.cls = b.x; p.orig = b.y; p.gid = b.z;
     return p;
 }
 
-// score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145)
-template <int NPL, bool CLK>
-__global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
+// score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145).
+// Pods are taken four at a time: a per-chunk summary says whether the four share group and class
+// with ascending memory values; if so and no lane's validity bound is crossed by the largest of
+// the four, all four inherit the warp's current (highest, lowest) with one test.
+#define SCORE_BLK 4
+template <int NPL>
+__global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
                                                             const u32 *__restrict__ tables, u64 *hilo) {
     __shared__ uint4 sp[HOT_CHUNK * 2];
-    __shared__ u32 hi_s[HOT_WARPS][HOT_CHUNK], lo_s[HOT_WARPS][HOT_CHUNK];
+    __shared__ uint4 blk[HOT_CHUNK / SCORE_BLK];  // gid (or ~0 if mixed), cls, first m, last m
+    __shared__ __align__(16) u32 hi_s[HOT_WARPS][HOT_CHUNK], lo_s[HOT_WARPS][HOT_CHUNK];
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const u32 c0 = p_begin + blockIdx.y * HOT_CHUNK;
     const u32 cn = min(HOT_CHUNK, p_end - c0);
     for (u32 i = threadIdx.x; i < cn * 2; i += HOT_THREADS) sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
     const u32 base = (blockIdx.x * HOT_WARPS + warp) * (NPL * 32);
-    NodeRegs<NPL, CLK> r;
+    NodeRegs<NPL> r;
     hot_load_nodes(r, s, base, lane);
     __syncthreads();
-    u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFFu, cur_m = 0;
+    if (threadIdx.x < HOT_CHUNK / SCORE_BLK) {
+        const u32 b0 = threadIdx.x * SCORE_BLK;
+        uint4 v = make_uint4(0xFFFFFFFFu, 0, 0, 0);
+        if (b0 + SCORE_BLK <= cn) {
+            const uint4 a0 = sp[2 * b0], c1 = sp[2 * b0 + 1];
+            bool ok = true;
+            u32 prev = a0.x;
+#pragma unroll
+            for (int k = 1; k < SCORE_BLK; ++k) {
+                const uint4 a = sp[2 * (b0 + k)], c = sp[2 * (b0 + k) + 1];
+                ok = ok && c.z == c1.z && c.x == c1.x && a.x >= prev;
+                prev = a.x;
+            }
+            if (ok) v = make_uint4(c1.z, c1.x, a0.x, prev);
+        }
+        blk[threadIdx.x] = v;
+    }
+    __syncthreads();
+    u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFEu, cur_m = 0;
     u32 hi_l[NPL], lo_l[NPL], bound[NPL];
 #pragma unroll
     for (int j = 0; j < NPL; ++j) { hi_l[j] = 0; lo_l[j] = 0xFFFFFFFFu; bound[j] = 0; }
     u32 hi_w = 0, lo_w = 0xFFFFFFFFu, bmin = 0;  // bmin = min over the lane's slots of bound[j]
-    for (u32 i = 0; i < cn; ++i) {
-        const PodRegs pod = pod_from_smem(sp, i);
-        const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
-        if (!same || __any_sync(0xFFFFFFFFu, pod.m > bmin)) {
-            if (pod.cls != cur_cls) hot_load_class(r, s, tables, pod.cls, base, lane);
-            cur_cls = pod.cls; cur_gid = pod.gid;
-#pragma unroll
-            for (int j = 0; j < NPL; ++j) {
-                if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
-                    bool fit;
-                    u32 b;
-                    const u32 raw = hot_eval(r, j, pod.m, pod.c, pod.num, pod.reqM, pod.reqC, fit, b);
-                    bound[j] = fit ? b : 0xFFFFFFFFu;
-                    hi_l[j] = fit ? raw : 0u;
-                    lo_l[j] = fit ? raw : 0xFFFFFFFFu;
-                }
+    for (u32 i0 = 0; i0 < cn; i0 += SCORE_BLK) {
+        const uint4 bs = blk[i0 / SCORE_BLK];
+        if (bs.x == cur_gid && bs.y == cur_cls && bs.z >= cur_m && !__any_sync(0xFFFFFFFFu, bs.w > bmin)) {
+            cur_m = bs.w;
+            if (lane == 0) {
+                *reinterpret_cast<uint4 *>(&hi_s[warp][i0]) = make_uint4(hi_w, hi_w, hi_w, hi_w);
+                *reinterpret_cast<uint4 *>(&lo_s[warp][i0]) = make_uint4(lo_w, lo_w, lo_w, lo_w);
             }
-            u32 hi = hi_l[0], lo = lo_l[0];
-            bmin = bound[0];
-#pragma unroll
-            for (int j = 1; j < NPL; ++j) { hi = max(hi, hi_l[j]); lo = min(lo, lo_l[j]); bmin = min(bmin, bound[j]); }
-            hi_w = __reduce_max_sync(0xFFFFFFFFu, hi);
-            lo_w = __reduce_min_sync(0xFFFFFFFFu, lo);
+            continue;
         }
-        cur_m = pod.m;
-        if (lane == 0) {
-            hi_s[warp][i] = hi_w;
-            lo_s[warp][i] = lo_w;
+        const u32 i1 = min(cn, i0 + SCORE_BLK);
+        for (u32 i = i0; i < i1; ++i) {
+            const PodRegs pod = pod_from_smem(sp, i);
+            const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
+            if (!same || __any_sync(0xFFFFFFFFu, pod.m > bmin)) {
+                if (pod.cls != cur_cls || pod.gid != cur_gid) hot_load_class(r, s, tables, pod.cls, pod.has_clock, pod.c, pod.reqC, base, lane);
+                cur_cls = pod.cls; cur_gid = pod.gid;
+#pragma unroll
+                for (int j = 0; j < NPL; ++j) {
+                    if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
+                        bool fit;
+                        u32 b;
+                        const u32 raw = hot_eval(r, j, pod.m, pod.num, pod.reqM, fit, b);
+                        bound[j] = fit ? b : 0xFFFFFFFFu;
+                        hi_l[j] = fit ? raw : 0u;
+                        lo_l[j] = fit ? raw : 0xFFFFFFFFu;
+                    }
+                }
+                u32 hi = hi_l[0], lo = lo_l[0];
+                bmin = bound[0];
+#pragma unroll
+                for (int j = 1; j < NPL; ++j) { hi = max(hi, hi_l[j]); lo = min(lo, lo_l[j]); bmin = min(bmin, bound[j]); }
+                hi_w = __reduce_max_sync(0xFFFFFFFFu, hi);
+                lo_w = __reduce_min_sync(0xFFFFFFFFu, lo);
+            }
+            cur_m = pod.m;
+            if (lane == 0) {
+                hi_s[warp][i] = hi_w;
+                lo_s[warp][i] = lo_w;
+            }
         }
     }
     __syncthreads();
@@ -542,8 +591,8 @@ __global__ void k_norm_prep(const PodS *__restrict__ pods, u32 P, const u64 *__r
 // output pass: feasible bits, Score (int64), NormalizeScore (uint8), feasible count, node choice.
 // Rows are padded to the CTA tile (stride % (HOT_WARPS*NPL*32) == 0), so no lane is out of range:
 // lanes past the last node hold no SCV, score 0 and write into the padding.
-template <int NPL, bool CLK, bool WRITE>
-__global__ void __launch_bounds__(HOT_THREADS) k_fast_out(DevSnap s, const PodS *__restrict__ pods, const PodNrm *__restrict__ nrm,
+template <int NPL, bool WRITE>
+__global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_out(DevSnap s, const PodS *__restrict__ pods, const PodNrm *__restrict__ nrm,
                                                           u32 p_begin, u32 p_end, const u32 *__restrict__ tables, u64 *count, u64 *ckey,
                                                           i64 *raw_out, u8 *norm_out, u32 *bits_out, u64 stride) {
     __shared__ uint4 sp[HOT_CHUNK * 2];
@@ -556,7 +605,7 @@ __global__ void __launch_bounds__(HOT_THREADS) k_fast_out(DevSnap s, const PodS 
     for (u32 i = threadIdx.x; i < cn * 2; i += HOT_THREADS) sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
     for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) sn[i] = reinterpret_cast<const uint4 *>(nrm + c0)[i];
     const u32 base = (blockIdx.x * HOT_WARPS + warp) * (NPL * 32);
-    NodeRegs<NPL, CLK> r;
+    NodeRegs<NPL> r;
     hot_load_nodes(r, s, base, lane);
     __syncthreads();
     u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFFu, cur_m = 0, cur_lo = 0, cur_hi = 0;
@@ -576,7 +625,7 @@ __global__ void __launch_bounds__(HOT_THREADS) k_fast_out(DevSnap s, const PodS 
         const bool nsame = same && (pn.x == cur_lo) && (pn.y == cur_hi);
         const bool miss_any = !same || __any_sync(0xFFFFFFFFu, pod.m > bmin);
         if (miss_any) {
-            if (pod.cls != cur_cls) hot_load_class(r, s, tables, pod.cls, base, lane);
+            if (pod.cls != cur_cls || pod.gid != cur_gid) hot_load_class(r, s, tables, pod.cls, pod.has_clock, pod.c, pod.reqC, base, lane);
             cur_cls = pod.cls; cur_gid = pod.gid;
             cnt = 0; wmax = 0;
 #pragma unroll
@@ -584,7 +633,7 @@ __global__ void __launch_bounds__(HOT_THREADS) k_fast_out(DevSnap s, const PodS 
                 if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
                     bool fit;
                     u32 b;
-                    const u32 raw = hot_eval(r, j, pod.m, pod.c, pod.num, pod.reqM, pod.reqC, fit, b);
+                    const u32 raw = hot_eval(r, j, pod.m, pod.num, pod.reqM, fit, b);
                     bound[j] = fit ? b : 0xFFFFFFFFu;
                     raw64[j] = raw;  // filter.go:84-86 is the identity below 2^63
                     fitm[j] = __ballot_sync(0xFFFFFFFFu, fit);

@@ -144,7 +144,7 @@ struct yoda_ctx {
     u32 *fw_m_sorted = nullptr, *fw_step = nullptr, *fw_cls_max = nullptr, *fw_tables = nullptr;
     u32 fw_tables_classes = 0;
     FastCtl *fw_ctl = nullptr, *fw_hctl = nullptr;
-    u32 fw_n_groups = 0, fw_n_classes = 0, fw_p0 = 0;
+    u32 fw_n_groups = 0, fw_n_classes = 0;
 };
 
 #define FAST_CLASS_CAP 4096u
@@ -611,26 +611,24 @@ static int fast_phase0(yoda_ctx *c) {
     return YODA_OK;
 }
 
-template <bool CLK>
 static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
     constexpr int NPL = 4;
     dim3 grid((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (p_end - p_begin + HOT_CHUNK - 1) / HOT_CHUNK);
-    k_fast_score<NPL, CLK><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo);
+    k_fast_score<NPL><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo);
     LAUNCHED(c);
     return YODA_OK;
 }
 
-template <bool CLK>
 static int fast_out_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
     constexpr int NPL = 4;
     dim3 grid((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (p_end - p_begin + HOT_CHUNK - 1) / HOT_CHUNK);
     if (c->ph_flags & YODA_EVAL_FULL)
-        k_fast_out<NPL, CLK, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->fw_nrm, p_begin, p_end, c->fw_tables,
+        k_fast_out<NPL, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->fw_nrm, p_begin, p_end, c->fw_tables,
                                                                         c->d_count, c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride);
     else
-        k_fast_out<NPL, CLK, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->fw_nrm, p_begin, p_end, c->fw_tables,
+        k_fast_out<NPL, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->fw_nrm, p_begin, p_end, c->fw_tables,
                                                                          c->d_count, c->d_ckey, nullptr, nullptr, nullptr, c->stride);
     LAUNCHED(c);
     return YODA_OK;
@@ -652,7 +650,6 @@ static int fast_phase1(yoda_ctx *c) {
     LAUNCHED(c);
     TRY(fast_read_ctl(c));
     c->fw_n_classes = c->fw_hctl->n_classes;
-    c->fw_p0 = std::min(c->fw_hctl->p0, P);
     if (c->fw_hctl->err || c->fw_n_classes > ccap) {
         c->ph_path = 0;
         return YODA_OK;
@@ -674,8 +671,7 @@ static int fast_phase1(yoda_ctx *c) {
         c->ph_path = 0;
         return YODA_OK;
     }
-    TRY(fast_score_launch<false>(c, 0, c->fw_p0));
-    TRY(fast_score_launch<true>(c, c->fw_p0, P));
+    TRY(fast_score_launch(c, 0, P));
     return YODA_OK;
 }
 
@@ -683,8 +679,7 @@ static int fast_phase2(yoda_ctx *c) {
     const u32 P = c->ph_P;
     k_norm_prep<<<(P + 255) / 256, 256, 0, c->stream>>>(c->fw_pods, P, c->d_hilo, c->fw_nrm);
     LAUNCHED(c);
-    TRY(fast_out_launch<false>(c, 0, c->fw_p0));
-    TRY(fast_out_launch<true>(c, c->fw_p0, P));
+    TRY(fast_out_launch(c, 0, P));
     return YODA_OK;
 }
 
