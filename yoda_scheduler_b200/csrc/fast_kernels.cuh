@@ -29,10 +29,6 @@ struct PodS {
     u32 gid;        // requirement group
     u32 pad;
 };
-// rescale constants of one pod for the output pass: norm = ((raw - lo) * 100 * M) >> 57
-struct PodNrm {
-    u32 lo, hi, mhi, mlo;
-};
 struct GroupDesc {
     u32 flags, c, num, seg_start, seg_end, pad0, pad1, pad2;
 };
@@ -469,61 +465,71 @@ __device__ __forceinline__ PodRegs pod_from_smem(const uint4 *sp, u32 i) {
     return p;
 }
 
+// Both passes are written as bodies over HOT_THREADS threads with their own shared memory and a
+// named barrier, so that they can be composed (a fused output+score CTA was tried in round 1 and
+// dropped: both passes need ~128 registers per thread, so they only time-share the SM).
+__device__ __forceinline__ void half_sync(int bar_id) { asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(HOT_THREADS) : "memory"); }
+
+#define SCORE_BLK 4
+struct ScoreSmem {
+    uint4 sp[HOT_CHUNK * 2];
+    uint4 blk[HOT_CHUNK / SCORE_BLK];  // gid (or ~0 if mixed), cls, first m, last m of four consecutive pods
+    __align__(16) u32 hi_s[HOT_WARPS][HOT_CHUNK];
+    __align__(16) u32 lo_s[HOT_WARPS][HOT_CHUNK];
+};
+
 // score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145).
 // Pods are taken four at a time: a per-chunk summary says whether the four share group and class
 // with ascending memory values; if so and no lane's validity bound is crossed by the largest of
 // the four, all four inherit the warp's current (highest, lowest) with one test.
-#define SCORE_BLK 4
 template <int NPL>
-__global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
-                                                            const u32 *__restrict__ tables, u64 *hilo) {
-    __shared__ uint4 sp[HOT_CHUNK * 2];
-    __shared__ uint4 blk[HOT_CHUNK / SCORE_BLK];  // gid (or ~0 if mixed), cls, first m, last m
-    __shared__ __align__(16) u32 hi_s[HOT_WARPS][HOT_CHUNK], lo_s[HOT_WARPS][HOT_CHUNK];
-    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const u32 c0 = p_begin + blockIdx.y * HOT_CHUNK;
+__device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u32 tile, u32 chunk, const DevSnap &s,
+                                           const PodS *__restrict__ pods, u32 p_begin, u32 p_end, const u32 *__restrict__ tables,
+                                           u64 *hilo) {
+    const u32 lane = tid & 31, warp = tid >> 5;
+    const u32 c0 = p_begin + chunk * HOT_CHUNK;
     const u32 cn = min(HOT_CHUNK, p_end - c0);
-    for (u32 i = threadIdx.x; i < cn * 2; i += HOT_THREADS) sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
-    const u32 base = (blockIdx.x * HOT_WARPS + warp) * (NPL * 32);
+    for (u32 i = tid; i < cn * 2; i += HOT_THREADS) sm.sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
+    const u32 base = (tile * HOT_WARPS + warp) * (NPL * 32);
     NodeRegs<NPL> r;
     hot_load_nodes(r, s, base, lane);
-    __syncthreads();
-    if (threadIdx.x < HOT_CHUNK / SCORE_BLK) {
-        const u32 b0 = threadIdx.x * SCORE_BLK;
+    half_sync(bar_id);
+    if (tid < HOT_CHUNK / SCORE_BLK) {
+        const u32 b0 = tid * SCORE_BLK;
         uint4 v = make_uint4(0xFFFFFFFFu, 0, 0, 0);
         if (b0 + SCORE_BLK <= cn) {
-            const uint4 a0 = sp[2 * b0], c1 = sp[2 * b0 + 1];
+            const uint4 a0 = sm.sp[2 * b0], c1 = sm.sp[2 * b0 + 1];
             bool ok = true;
             u32 prev = a0.x;
 #pragma unroll
             for (int k = 1; k < SCORE_BLK; ++k) {
-                const uint4 a = sp[2 * (b0 + k)], c = sp[2 * (b0 + k) + 1];
+                const uint4 a = sm.sp[2 * (b0 + k)], c = sm.sp[2 * (b0 + k) + 1];
                 ok = ok && c.z == c1.z && c.x == c1.x && a.x >= prev;
                 prev = a.x;
             }
             if (ok) v = make_uint4(c1.z, c1.x, a0.x, prev);
         }
-        blk[threadIdx.x] = v;
+        sm.blk[tid] = v;
     }
-    __syncthreads();
+    half_sync(bar_id);
     u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFEu, cur_m = 0;
     u32 hi_l[NPL], lo_l[NPL], bound[NPL];
 #pragma unroll
     for (int j = 0; j < NPL; ++j) { hi_l[j] = 0; lo_l[j] = 0xFFFFFFFFu; bound[j] = 0; }
     u32 hi_w = 0, lo_w = 0xFFFFFFFFu, bmin = 0;  // bmin = min over the lane's slots of bound[j]
     for (u32 i0 = 0; i0 < cn; i0 += SCORE_BLK) {
-        const uint4 bs = blk[i0 / SCORE_BLK];
+        const uint4 bs = sm.blk[i0 / SCORE_BLK];
         if (bs.x == cur_gid && bs.y == cur_cls && bs.z >= cur_m && !__any_sync(0xFFFFFFFFu, bs.w > bmin)) {
             cur_m = bs.w;
             if (lane == 0) {
-                *reinterpret_cast<uint4 *>(&hi_s[warp][i0]) = make_uint4(hi_w, hi_w, hi_w, hi_w);
-                *reinterpret_cast<uint4 *>(&lo_s[warp][i0]) = make_uint4(lo_w, lo_w, lo_w, lo_w);
+                *reinterpret_cast<uint4 *>(&sm.hi_s[warp][i0]) = make_uint4(hi_w, hi_w, hi_w, hi_w);
+                *reinterpret_cast<uint4 *>(&sm.lo_s[warp][i0]) = make_uint4(lo_w, lo_w, lo_w, lo_w);
             }
             continue;
         }
         const u32 i1 = min(cn, i0 + SCORE_BLK);
         for (u32 i = i0; i < i1; ++i) {
-            const PodRegs pod = pod_from_smem(sp, i);
+            const PodRegs pod = pod_from_smem(sm.sp, i);
             const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
             if (!same || __any_sync(0xFFFFFFFFu, pod.m > bmin)) {
                 if (pod.cls != cur_cls || pod.gid != cur_gid) hot_load_class(r, s, tables, pod.cls, pod.has_clock, pod.c, pod.reqC, base, lane);
@@ -548,69 +554,66 @@ __global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_score(DevSnap s, const 
             }
             cur_m = pod.m;
             if (lane == 0) {
-                hi_s[warp][i] = hi_w;
-                lo_s[warp][i] = lo_w;
+                sm.hi_s[warp][i] = hi_w;
+                sm.lo_s[warp][i] = lo_w;
             }
         }
     }
-    __syncthreads();
-    for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) {
+    half_sync(bar_id);
+    for (u32 i = tid; i < cn; i += HOT_THREADS) {
         u32 hi = 0, lo = 0xFFFFFFFFu;
 #pragma unroll
         for (int w = 0; w < HOT_WARPS; ++w) {
-            hi = max(hi, hi_s[w][i]);
-            lo = min(lo, lo_s[w][i]);
+            hi = max(hi, sm.hi_s[w][i]);
+            lo = min(lo, sm.lo_s[w][i]);
         }
         if (lo != 0xFFFFFFFFu) {  // some node of this tile is feasible
-            const u32 orig = sp[2 * i + 1].y;
+            const u32 orig = sm.sp[2 * i + 1].y;
             atomicMax(&hilo[2 * (size_t)orig], (u64)hi);
             atomicMax(&hilo[2 * (size_t)orig + 1], ~(u64)lo);
         }
     }
 }
 
-// rescale constants per sorted pod, from the (cross-shard reduced) lowest/highest
-__global__ void k_norm_prep(const PodS *__restrict__ pods, u32 P, const u64 *__restrict__ hilo, PodNrm *out) {
-    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P) return;
-    const u32 orig = pods[i].orig;
-    PodNrm r;
-    if (hilo[2 * (size_t)orig + 1] == 0) {  // no feasible node anywhere
-        r.lo = 0; r.hi = 0xFFFFFFFFu; r.mhi = 0; r.mlo = 0;
-    } else {
-        const u32 hi = (u32)hilo[2 * (size_t)orig];
-        u32 lo = (u32)(~hilo[2 * (size_t)orig + 1]);
-        if (hi == lo) lo = lo - 1u;  // scheduler.go:147-149 (may become -1 = 0xFFFFFFFF)
-        const u32 d = hi - lo;       // 1 .. 2^25
-        const u64 M = ((1ull << 57) / d) + 1ull;
-        r.lo = lo; r.hi = hi; r.mhi = (u32)(M >> 32); r.mlo = (u32)M;
-    }
-    out[i] = r;
+struct OutSmem {
+    uint4 sp[HOT_CHUNK * 2];
+    uint4 sn[HOT_CHUNK];  // rescale constants per pod: lo, hi, reciprocal hi/lo words
+    u32 cnt_s[HOT_WARPS][HOT_CHUNK];
+    u32 best_s[HOT_WARPS][HOT_CHUNK];
+};
+
+// rescale constants of one pod from the (cross-shard reduced) lowest/highest: norm = ((raw-lo)*100*M) >> 57
+__device__ __forceinline__ uint4 norm_consts(const u64 *__restrict__ hilo, u32 orig) {
+    const u64 nlo = hilo[2 * (size_t)orig + 1];
+    if (nlo == 0) return make_uint4(0, 0xFFFFFFFFu, 0, 0);  // no feasible node anywhere
+    const u32 hi = (u32)hilo[2 * (size_t)orig];
+    u32 lo = (u32)(~nlo);
+    if (hi == lo) lo = lo - 1u;  // scheduler.go:147-149 (may become -1 = 0xFFFFFFFF)
+    const u32 d = hi - lo;       // 1 .. 2^25
+    const u64 M = ((1ull << 57) / d) + 1ull;
+    return make_uint4(lo, hi, (u32)(M >> 32), (u32)M);
 }
 
 // output pass: feasible bits, Score (int64), NormalizeScore (uint8), feasible count, node choice.
 // Rows are padded to the CTA tile (stride % (HOT_WARPS*NPL*32) == 0), so no lane is out of range:
 // lanes past the last node hold no SCV, score 0 and write into the padding.
 template <int NPL, bool WRITE>
-__global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_out(DevSnap s, const PodS *__restrict__ pods, const PodNrm *__restrict__ nrm,
-                                                          u32 p_begin, u32 p_end, const u32 *__restrict__ tables, u64 *count, u64 *ckey,
-                                                          i64 *raw_out, u8 *norm_out, u32 *bits_out, u64 stride) {
-    __shared__ uint4 sp[HOT_CHUNK * 2];
-    __shared__ uint4 sn[HOT_CHUNK];
-    __shared__ u32 cnt_s[HOT_WARPS][HOT_CHUNK];
-    __shared__ u32 best_s[HOT_WARPS][HOT_CHUNK];
-    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const u32 c0 = p_begin + blockIdx.y * HOT_CHUNK;
+__device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 tile, u32 chunk, const DevSnap &s,
+                                         const PodS *__restrict__ pods, const u64 *__restrict__ hilo, u32 p_begin, u32 p_end,
+                                         const u32 *__restrict__ tables, u64 *count, u64 *ckey, i64 *raw_out, u8 *norm_out, u32 *bits_out,
+                                         u64 stride) {
+    const u32 lane = tid & 31, warp = tid >> 5;
+    const u32 c0 = p_begin + chunk * HOT_CHUNK;
     const u32 cn = min(HOT_CHUNK, p_end - c0);
-    for (u32 i = threadIdx.x; i < cn * 2; i += HOT_THREADS) sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
-    for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) sn[i] = reinterpret_cast<const uint4 *>(nrm + c0)[i];
-    const u32 base = (blockIdx.x * HOT_WARPS + warp) * (NPL * 32);
+    for (u32 i = tid; i < cn * 2; i += HOT_THREADS) sm.sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
+    for (u32 i = tid; i < cn; i += HOT_THREADS) sm.sn[i] = norm_consts(hilo, pods[c0 + i].orig);
+    const u32 base = (tile * HOT_WARPS + warp) * (NPL * 32);
     NodeRegs<NPL> r;
     hot_load_nodes(r, s, base, lane);
-    __syncthreads();
-    u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFFu, cur_m = 0, cur_lo = 0, cur_hi = 0;
-    u64 raw64[NPL];                 // Score as stored (int64, high word 0)
-    u32 bound[NPL], fitm[NPL];      // validity bound per lane; feasible lanes of the slot (warp-uniform)
+    half_sync(bar_id);
+    u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFEu, cur_m = 0, cur_lo = 0, cur_hi = 0;
+    u64 raw64[NPL];                     // Score as stored (int64, high word 0)
+    u32 bound[NPL], fitm[NPL];          // validity bound per lane; feasible lanes of the slot (warp-uniform)
     u32 fitl[NPL], qn[NPL], rmax[NPL];  // lane mask (0 / ~0), normalized score, best feasible score of the slot
 #pragma unroll
     for (int j = 0; j < NPL; ++j) { raw64[j] = 0; bound[j] = 0; fitm[j] = 0; fitl[j] = 0; qn[j] = 0; rmax[j] = 0; }
@@ -619,8 +622,8 @@ __global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_out(DevSnap s, const Po
     u8 *normp = norm_out + base + lane;
     u32 *bitsp = bits_out + (base >> 5);
     for (u32 i = 0; i < cn; ++i) {
-        const PodRegs pod = pod_from_smem(sp, i);
-        const uint4 pn = sn[i];  // lo, hi, mhi, mlo
+        const PodRegs pod = pod_from_smem(sm.sp, i);
+        const uint4 pn = sm.sn[i];  // lo, hi, mhi, mlo
         const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
         const bool nsame = same && (pn.x == cur_lo) && (pn.y == cur_hi);
         const bool miss_any = !same || __any_sync(0xFFFFFFFFu, pod.m > bmin);
@@ -685,20 +688,36 @@ __global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_out(DevSnap s, const Po
             }
         }
         if (lane == 0) {
-            cnt_s[warp][i] = cnt;
-            best_s[warp][i] = best;
+            sm.cnt_s[warp][i] = cnt;
+            sm.best_s[warp][i] = best;
         }
     }
-    __syncthreads();
-    for (u32 i = threadIdx.x; i < cn; i += HOT_THREADS) {
+    half_sync(bar_id);
+    for (u32 i = tid; i < cn; i += HOT_THREADS) {
         u32 cnt2 = 0, best = 0xFFFFFFFFu;
 #pragma unroll
         for (int w = 0; w < HOT_WARPS; ++w) {
-            cnt2 += cnt_s[w][i];
-            best = min(best, best_s[w][i]);
+            cnt2 += sm.cnt_s[w][i];
+            best = min(best, sm.best_s[w][i]);
         }
-        const u32 orig = sp[2 * i + 1].y;
+        const u32 orig = sm.sp[2 * i + 1].y;
         if (cnt2) atomicAdd(&count[orig], (u64)cnt2);
         if (best != 0xFFFFFFFFu) atomicMax(&ckey[orig], ckey_of(s.node_base + best));
     }
+}
+
+template <int NPL>
+__global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
+                                                               const u32 *__restrict__ tables, u64 *hilo) {
+    __shared__ ScoreSmem sm;
+    score_body<NPL>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo);
+}
+
+template <int NPL, bool WRITE>
+__global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_out(DevSnap s, const PodS *__restrict__ pods, const u64 *__restrict__ hilo,
+                                                             u32 p_begin, u32 p_end, const u32 *__restrict__ tables, u64 *count, u64 *ckey,
+                                                             i64 *raw_out, u8 *norm_out, u32 *bits_out, u64 stride) {
+    __shared__ OutSmem sm;
+    out_body<NPL, WRITE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, hilo, p_begin, p_end, tables, count, ckey, raw_out, norm_out,
+                         bits_out, stride);
 }

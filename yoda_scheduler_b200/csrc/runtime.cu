@@ -140,7 +140,6 @@ struct yoda_ctx {
     size_t fw_cub_bytes = 0;
     GroupDesc *fw_gdesc = nullptr;
     PodS *fw_pods = nullptr;
-    PodNrm *fw_nrm = nullptr;
     u32 *fw_m_sorted = nullptr, *fw_step = nullptr, *fw_cls_max = nullptr, *fw_tables = nullptr;
     u32 fw_tables_classes = 0;
     FastCtl *fw_ctl = nullptr, *fw_hctl = nullptr;
@@ -267,7 +266,7 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     dev_free(c->d_raw); dev_free(c->d_norm); dev_free(c->d_bits);
     dev_free(c->fw_gkeys); dev_free(c->fw_ckeys); dev_free(c->fw_gids); dev_free(c->fw_cids); dev_free(c->fw_crep);
     dev_free(c->fw_slot); dev_free(c->fw_pod_gid); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
-    dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_gdesc); dev_free(c->fw_pods); dev_free(c->fw_nrm);
+    dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_gdesc); dev_free(c->fw_pods);
     dev_free(c->fw_m_sorted); dev_free(c->fw_step); dev_free(c->fw_cls_max); dev_free(c->fw_tables); dev_free(c->fw_ctl);
     if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
     if (c->fw_hctl) cudaFreeHost(c->fw_hctl);
@@ -494,7 +493,7 @@ static int ensure_fast(yoda_ctx *c, u32 P) {
     while (htab < 2 * cap) htab <<= 1;
     dev_free(c->fw_gkeys); dev_free(c->fw_ckeys); dev_free(c->fw_gids); dev_free(c->fw_cids); dev_free(c->fw_crep);
     dev_free(c->fw_slot); dev_free(c->fw_pod_gid); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
-    dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_pods); dev_free(c->fw_nrm);
+    dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_pods);
     dev_free(c->fw_m_sorted); dev_free(c->fw_step);
     if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
     c->fw_cub_tmp = nullptr;
@@ -511,7 +510,6 @@ static int ensure_fast(yoda_ctx *c, u32 P) {
     TRY(dev_alloc(&c->fw_vals_in, cap));
     TRY(dev_alloc(&c->fw_vals_out, cap));
     TRY(dev_alloc(&c->fw_pods, cap));
-    TRY(dev_alloc(&c->fw_nrm, cap));
     TRY(dev_alloc(&c->fw_m_sorted, cap));
     TRY(dev_alloc(&c->fw_step, (size_t)cap * 6));
     size_t bytes = 0;
@@ -611,31 +609,33 @@ static int fast_phase0(yoda_ctx *c) {
     return YODA_OK;
 }
 
+static dim3 hot_grid(const yoda_ctx *c, u32 n_pods) {
+    constexpr int NPL = 4;
+    return dim3((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (n_pods + HOT_CHUNK - 1) / HOT_CHUNK);
+}
+
 static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
-    constexpr int NPL = 4;
-    dim3 grid((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (p_end - p_begin + HOT_CHUNK - 1) / HOT_CHUNK);
-    k_fast_score<NPL><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo);
+    k_fast_score<4><<<hot_grid(c, p_end - p_begin), HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo);
     LAUNCHED(c);
     return YODA_OK;
 }
 
 static int fast_out_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
-    constexpr int NPL = 4;
-    dim3 grid((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (p_end - p_begin + HOT_CHUNK - 1) / HOT_CHUNK);
+    const dim3 grid = hot_grid(c, p_end - p_begin);
     if (c->ph_flags & YODA_EVAL_FULL)
-        k_fast_out<NPL, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->fw_nrm, p_begin, p_end, c->fw_tables,
-                                                                        c->d_count, c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride);
+        k_fast_out<4, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
+                                                                 c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride);
     else
-        k_fast_out<NPL, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->fw_nrm, p_begin, p_end, c->fw_tables,
-                                                                         c->d_count, c->d_ckey, nullptr, nullptr, nullptr, c->stride);
+        k_fast_out<4, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
+                                                                  c->d_ckey, nullptr, nullptr, nullptr, c->stride);
     LAUNCHED(c);
     return YODA_OK;
 }
 
-// classes -> tables -> score reduce.  Returns with ph_path = 0 if the batch cannot use the tables.
-static int fast_phase1(yoda_ctx *c) {
+// classes -> tables.  Returns with ph_path = 0 if the batch cannot use the tables.
+static int fast_classes(yoda_ctx *c) {
     const u32 P = c->ph_P, N = c->snap.n_nodes;
     cudaStream_t st = c->stream;
     const u32 pb = (P + 255) / 256;
@@ -671,15 +671,6 @@ static int fast_phase1(yoda_ctx *c) {
         c->ph_path = 0;
         return YODA_OK;
     }
-    TRY(fast_score_launch(c, 0, P));
-    return YODA_OK;
-}
-
-static int fast_phase2(yoda_ctx *c) {
-    const u32 P = c->ph_P;
-    k_norm_prep<<<(P + 255) / 256, 256, 0, c->stream>>>(c->fw_pods, P, c->d_hilo, c->fw_nrm);
-    LAUNCHED(c);
-    TRY(fast_out_launch(c, 0, P));
     return YODA_OK;
 }
 
@@ -705,7 +696,8 @@ static int phase0(yoda_ctx *c, const yoda_pod_req *d_req) {
 
 // phase 1: local lowest/highest over feasible nodes
 static int phase1(yoda_ctx *c) {
-    if (c->ph_path == 1) TRY(fast_phase1(c));
+    if (c->ph_path == 1) TRY(fast_classes(c));
+    if (c->ph_path == 1) TRY(fast_score_launch(c, 0, c->ph_P));
     if (c->ph_path == 0) TRY(direct_pods_launch(c, 1));
     CU(cudaEventRecord(c->ev[EV_SCORE], c->stream));
     return YODA_OK;
@@ -713,7 +705,7 @@ static int phase1(yoda_ctx *c) {
 
 // phase 2: output pass (matrices when FULL), feasible counts, node choice
 static int phase2(yoda_ctx *c) {
-    if (c->ph_path == 1) return fast_phase2(c);
+    if (c->ph_path == 1) return fast_out_launch(c, 0, c->ph_P);
     return direct_out_launch(c);
 }
 
