@@ -446,6 +446,38 @@ __device__ __forceinline__ u32 hot_eval(const NodeRegs<NPL> &r, int j, u32 m, u3
     return r.stat[j] + (fit ? basic : 0u);    // algorithm.go:38 (no uint64 wrap in the narrow range)
 }
 
+// The same evaluation with the node's cards fetched on demand (L2) instead of held in registers:
+// used by the score pass, where re-evaluations are rare and a small register footprint (more
+// resident warps) matters more than their latency.
+__device__ __forceinline__ u32 hot_eval_mem(const DevSnap &s, const u32 *__restrict__ tables, u32 node, u32 cls, u32 m, u32 num, u32 reqM,
+                                            bool has_clock, u32 c, u32 reqC, bool ok, u32 cardnum, u32 stat, bool &fit, u32 &bound) {
+    u32 fr[G], cs[G];
+    load8(s.n32[F_FREE] + (size_t)node * G, fr);
+    load8(tables + ((size_t)cls * s.cap + node) * G, cs);
+    bool clkok = true;
+    if (has_clock) {  // warp-uniform; see hot_load_class
+        u32 ck[G];
+        load8(s.n32[F_CLOCK] + (size_t)node * G, ck);
+        u32 cnt = 0;
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            cnt += (ck[g] == c) ? (cs[g] >> CS_HEALTH_SHIFT) : 0u;
+            if (ck[g] < c) cs[g] &= ~CS_SCORE_MASK;
+        }
+        clkok = cnt >= reqC;
+    }
+    u32 acc = 0, b = 0xFFFFFFFFu;
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const bool q = fr[g] >= m;
+        b = q ? min(b, fr[g]) : b;
+        acc += q ? cs[g] : 0u;
+    }
+    bound = b;
+    fit = ok && clkok && (num <= cardnum) && ((acc >> CS_HEALTH_SHIFT) >= reqM);
+    return stat + (fit ? (acc & CS_SCORE_MASK) : 0u);
+}
+
 // The pods arrive sorted by (group, memory).  Along that order the verdict and score of a node
 // change only when the memory value crosses one of the node's FreeMemory values, so each lane
 // keeps its last result and the bound up to which it stays valid; a 32-node slot is re-evaluated
@@ -491,23 +523,32 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
     const u32 cn = min(HOT_CHUNK, p_end - c0);
     for (u32 i = tid; i < cn * 2; i += HOT_THREADS) sm.sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
     const u32 base = (tile * HOT_WARPS + warp) * (NPL * 32);
-    NodeRegs<NPL> r;
-    hot_load_nodes(r, s, base, lane);
+    u32 node[NPL], cardnum[NPL], stat[NPL];
+    bool ok[NPL];
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) {
+        const u32 n = base + j * 32 + lane;
+        const bool in = n < s.n_nodes;
+        node[j] = in ? n : 0;
+        cardnum[j] = s.cardnum32[node[j]];
+        stat[j] = in ? s.stat32[node[j]] : 0u;
+        ok[j] = in && (s.meta[node[j]] & META_HAS_SCV);
+    }
     half_sync(bar_id);
     if (tid < HOT_CHUNK / SCORE_BLK) {
         const u32 b0 = tid * SCORE_BLK;
         uint4 v = make_uint4(0xFFFFFFFFu, 0, 0, 0);
         if (b0 + SCORE_BLK <= cn) {
             const uint4 a0 = sm.sp[2 * b0], c1 = sm.sp[2 * b0 + 1];
-            bool ok = true;
+            bool okb = true;
             u32 prev = a0.x;
 #pragma unroll
             for (int k = 1; k < SCORE_BLK; ++k) {
                 const uint4 a = sm.sp[2 * (b0 + k)], c = sm.sp[2 * (b0 + k) + 1];
-                ok = ok && c.z == c1.z && c.x == c1.x && a.x >= prev;
+                okb = okb && c.z == c1.z && c.x == c1.x && a.x >= prev;
                 prev = a.x;
             }
-            if (ok) v = make_uint4(c1.z, c1.x, a0.x, prev);
+            if (okb) v = make_uint4(c1.z, c1.x, a0.x, prev);
         }
         sm.blk[tid] = v;
     }
@@ -532,14 +573,14 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
             const PodRegs pod = pod_from_smem(sm.sp, i);
             const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
             if (!same || __any_sync(0xFFFFFFFFu, pod.m > bmin)) {
-                if (pod.cls != cur_cls || pod.gid != cur_gid) hot_load_class(r, s, tables, pod.cls, pod.has_clock, pod.c, pod.reqC, base, lane);
                 cur_cls = pod.cls; cur_gid = pod.gid;
 #pragma unroll
                 for (int j = 0; j < NPL; ++j) {
                     if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
                         bool fit;
                         u32 b;
-                        const u32 raw = hot_eval(r, j, pod.m, pod.num, pod.reqM, fit, b);
+                        const u32 raw = hot_eval_mem(s, tables, node[j], pod.cls, pod.m, pod.num, pod.reqM, pod.has_clock, pod.c, pod.reqC, ok[j],
+                                                     cardnum[j], stat[j], fit, b);
                         bound[j] = fit ? b : 0xFFFFFFFFu;
                         hi_l[j] = fit ? raw : 0u;
                         lo_l[j] = fit ? raw : 0xFFFFFFFFu;
@@ -675,12 +716,12 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
             const size_t row = (size_t)pod.orig * stride;
 #pragma unroll
             for (int j = 0; j < NPL; ++j) {
-                rawp[row + j * 32] = raw64[j];
-                normp[row + j * 32] = (u8)qn[j];
+                __stcs(rawp + row + j * 32, raw64[j]);   // streaming: written once, never re-read by this pass
+                __stcs(normp + row + j * 32, (u8)qn[j]);
             }
             if (lane == 0) {
                 u32 *bp = bitsp + (size_t)pod.orig * (stride >> 5);
-                if (NPL == 4) *reinterpret_cast<uint4 *>(bp) = make_uint4(fitm[0], fitm[1], fitm[2], fitm[3]);
+                if (NPL == 4) __stcs(reinterpret_cast<uint4 *>(bp), make_uint4(fitm[0], fitm[1], fitm[2], fitm[3]));
                 else if (NPL == 2) *reinterpret_cast<uint2 *>(bp) = make_uint2(fitm[0], fitm[1]);
                 else
 #pragma unroll
@@ -707,7 +748,7 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
 }
 
 template <int NPL>
-__global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
+__global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
                                                                const u32 *__restrict__ tables, u64 *hilo) {
     __shared__ ScoreSmem sm;
     score_body<NPL>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo);
