@@ -55,6 +55,11 @@ __device__ __forceinline__ u64 mix64(u64 z) {
     return z ^ (z >> 31);
 }
 
+__device__ __forceinline__ void load8(const u32 *p, u32 *dst) {
+    const uint4 a = reinterpret_cast<const uint4 *>(p)[0], b = reinterpret_cast<const uint4 *>(p)[1];
+    dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; dst[3] = a.w; dst[4] = b.x; dst[5] = b.y; dst[6] = b.z; dst[7] = b.w;
+}
+
 // ------------------------------------------------------------------------------------------
 // open-addressing set of 64-bit keys; empty = all ones.  Insert only publishes the key; dense ids
 // are handed out by k_hash_compact, so no thread ever waits on another.
@@ -173,64 +178,84 @@ __global__ void k_build_sorted(const PodC *__restrict__ pods, u32 P, const u64 *
 // k_max_scan turns that into the maxima of all cards admissible for pod i.
 // ------------------------------------------------------------------------------------------
 #define MAXT 128
+#define MAXG_TILE 8  // group descriptors staged per shared-memory tile
 __global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupDesc *__restrict__ gdesc, u32 n_groups,
                                                          const u32 *__restrict__ m_sorted, u32 *step, u32 P) {
-    const u32 gid = blockIdx.y;
+    __shared__ GroupDesc sg[MAXG_TILE];
     const u32 n = blockIdx.x * MAXT + threadIdx.x;
-    if (gid >= n_groups || n >= s.n_nodes) return;
-    const GroupDesc gd = gdesc[gid];
-    const u32 meta = s.meta[n];
-    if (!(meta & META_HAS_SCV)) return;
-    if (gd.num > s.cardnum32[n]) return;  // filter.go:13,15
+    const bool live = n < s.n_nodes;
+    const u32 nn = live ? n : 0;
+    const u32 meta = live ? s.meta[nn] : 0u;
+    const bool has = (meta & META_HAS_SCV) != 0;
     const u32 nc = meta_ncards(meta), hm = meta_healthy(meta);
+    const u32 cardnum = s.cardnum32[nn];
     u32 fr[G], ck[G];
-    const uint4 *pf = reinterpret_cast<const uint4 *>(s.n32[F_FREE] + (size_t)n * G);
-    const uint4 *pc = reinterpret_cast<const uint4 *>(s.n32[F_CLOCK] + (size_t)n * G);
-    uint4 a = pf[0], b = pf[1];
-    fr[0] = a.x; fr[1] = a.y; fr[2] = a.z; fr[3] = a.w; fr[4] = b.x; fr[5] = b.y; fr[6] = b.z; fr[7] = b.w;
-    a = pc[0]; b = pc[1];
-    ck[0] = a.x; ck[1] = a.y; ck[2] = a.z; ck[3] = a.w; ck[4] = b.x; ck[5] = b.y; ck[6] = b.z; ck[7] = b.w;
-    if (gd.flags & YODA_POD_HAS_CLOCK) {  // filter.go:35-50
-        u32 cnt = 0;
+    load8(s.n32[F_FREE] + (size_t)nn * G, fr);
+    load8(s.n32[F_CLOCK] + (size_t)nn * G, ck);
+    // Tk[k-1] = k-th largest FreeMemory among healthy cards: the node admits memory values m <= Tk[num-1]
+    // when scv/memory is present (filter.go:18-33)
+    u32 Tk[G];
 #pragma unroll
-        for (int g = 0; g < G; ++g) cnt += ((hm >> g) & 1u) & (u32)(ck[g] == gd.c);
-        if (cnt < gd.num) return;
+    for (int k = 0; k < G; ++k) Tk[k] = 0;
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        if ((hm >> g) & 1u) {
+            u32 rank = 0;
+#pragma unroll
+            for (int h = 0; h < G; ++h)
+                if (((hm >> h) & 1u) && (fr[h] > fr[g] || (fr[h] == fr[g] && h < g))) rank++;
+#pragma unroll
+            for (int k = 0; k < G; ++k)
+                if (rank == (u32)k) Tk[k] = fr[g];
+        }
     }
-    // node admits memory values m <= T: T = num-th largest FreeMemory among healthy cards (filter.go:18-33)
-    u32 T = 0xFFFFFFFFu;
-    if ((gd.flags & YODA_POD_HAS_MEMORY) && gd.num >= 1) {
-        if ((u32)__popc(hm) < gd.num) return;
-        T = 0;
+    const u32 n_healthy = __popc(hm);
+    // blockIdx.y takes every gridDim.y-th tile of groups
+    for (u32 g0 = blockIdx.y * MAXG_TILE; g0 < n_groups; g0 += MAXG_TILE * gridDim.y) {
+        __syncthreads();
+        if (threadIdx.x < MAXG_TILE && g0 + threadIdx.x < n_groups) sg[threadIdx.x] = gdesc[g0 + threadIdx.x];
+        __syncthreads();
+        const u32 gn = min(MAXG_TILE, n_groups - g0);
+        if (!has) continue;
+        for (u32 gi = 0; gi < gn; ++gi) {
+            const GroupDesc gd = sg[gi];
+            if (gd.num > cardnum) continue;  // filter.go:13,15
+            if (gd.flags & YODA_POD_HAS_CLOCK) {  // filter.go:35-50
+                u32 cnt = 0;
 #pragma unroll
-        for (int g = 0; g < G; ++g) {
-            if ((hm >> g) & 1u) {
-                u32 rank = 0;
+                for (int g = 0; g < G; ++g) cnt += ((hm >> g) & 1u) & (u32)(ck[g] == gd.c);
+                if (cnt < gd.num) continue;
+            }
+            u32 T = 0xFFFFFFFFu;
+            if ((gd.flags & YODA_POD_HAS_MEMORY) && gd.num >= 1) {
+                if (n_healthy < gd.num) continue;
+                T = 0;
 #pragma unroll
-                for (int h = 0; h < G; ++h)
-                    if (((hm >> h) & 1u) && (fr[h] > fr[g] || (fr[h] == fr[g] && h < g))) rank++;
-                if (rank == gd.num - 1) T = fr[g];
+                for (int k = 0; k < G; ++k)
+                    if (gd.num == (u32)(k + 1)) T = Tk[k];
+            }
+            const u32 *ms = m_sorted + gd.seg_start;
+            const u32 len = gd.seg_end - gd.seg_start;
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                if (g >= (int)nc || ck[g] < gd.c) continue;  // collection.go:46 (clock >= c; c == 0 without the label)
+                const u32 e = min(fr[g], T);
+                // j = number of pods of the group with memory <= e
+                u32 lo = 0, hi = len;
+                while (lo < hi) {
+                    const u32 mid = (lo + hi) >> 1;
+                    if (ms[mid] <= e) lo = mid + 1; else hi = mid;
+                }
+                if (lo == 0) continue;
+                const u32 pos = gd.seg_start + lo - 1;
+                const size_t o = (size_t)n * G + g;
+                // collection.go:59-78; order of the step planes = collection.MaxValue (bw, clock, core, free, power, total)
+                const u32 v[6] = {s.n32[F_BW][o], ck[g], s.n32[F_CORE][o], fr[g], s.n32[F_POWER][o], s.n32[F_TOTAL][o]};
+#pragma unroll
+                for (int f = 0; f < 6; ++f)
+                    if (v[f] > step[(size_t)f * P + pos]) atomicMax(&step[(size_t)f * P + pos], v[f]);
             }
         }
-    }
-    const u32 *ms = m_sorted + gd.seg_start;
-    const u32 len = gd.seg_end - gd.seg_start;
-    for (int g = 0; g < (int)nc; ++g) {
-        if (ck[g] < gd.c) continue;  // collection.go:46 (clock >= c; c == 0 without the label)
-        const u32 e = min(fr[g], T);
-        // j = number of pods of the group with memory <= e
-        u32 lo = 0, hi = len;
-        while (lo < hi) {
-            const u32 mid = (lo + hi) >> 1;
-            if (ms[mid] <= e) lo = mid + 1; else hi = mid;
-        }
-        if (lo == 0) continue;
-        const u32 pos = gd.seg_start + lo - 1;
-        const size_t o = (size_t)n * G + g;
-        // collection.go:59-78; order of the step planes = collection.MaxValue (bw, clock, core, free, power, total)
-        const u32 v[6] = {s.n32[F_BW][o], ck[g], s.n32[F_CORE][o], fr[g], s.n32[F_POWER][o], s.n32[F_TOTAL][o]};
-#pragma unroll
-        for (int f = 0; f < 6; ++f)
-            if (v[f] > step[(size_t)f * P + pos]) atomicMax(&step[(size_t)f * P + pos], v[f]);
     }
 }
 
@@ -316,10 +341,12 @@ __global__ void k_class_assign(PodS *pods, u32 P, const u64 *__restrict__ max6, 
     }
 }
 
-// exact floor(x * 100 / d) for x, d < 2^32, d >= 1
-__device__ __forceinline__ u32 div100(u32 x, u32 d, bool &big) {
+// exact floor(x * 100 / d) for x, d < 2^32, d >= 1, with the divisor's reciprocal M = ceil(2^64 / d)
+// (M == 0 stands for d == 1): mulhi(a, M) == floor(a / d) for every a < 2^32, because M*d = 2^64 + e with
+// 0 <= e < d and a*e < 2^64; larger a divide for real
+__device__ __forceinline__ u32 div100(u32 x, u32 d, u64 M, bool &big) {
     const u64 a = (u64)x * 100ull;
-    const u64 q = (a >> 32) ? a / (u64)d : (u64)((u32)a / d);
+    const u64 q = (a >> 32) ? a / (u64)d : (M ? __umul64hi(a, M) : a);
     big |= q >= CS_LIMIT;
     return (u32)q;
 }
@@ -330,11 +357,19 @@ __device__ __forceinline__ u32 div100(u32 x, u32 d, bool &big) {
 #define CLST 128
 __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__restrict__ cls_max, u32 n_classes, u32 *tables,
                                                        FastCtl *ctl) {
+    __shared__ u64 magic[6];
     const u32 cid = blockIdx.y;
+    if (cid >= n_classes) return;
+    if (threadIdx.x < 6) {
+        const u32 d = cls_max[cid * 6 + threadIdx.x];
+        magic[threadIdx.x] = d > 1 ? (0xFFFFFFFFFFFFFFFFull / d) + 1ull : 0ull;  // ceil(2^64 / d), also for powers of two
+    }
+    __syncthreads();
     const u32 n = blockIdx.x * CLST + threadIdx.x;
-    if (cid >= n_classes || n >= s.n_nodes) return;
+    if (n >= s.n_nodes) return;
     const u32 mbw = cls_max[cid * 6 + 0], mck = cls_max[cid * 6 + 1], mco = cls_max[cid * 6 + 2], mfr = cls_max[cid * 6 + 3],
               mpw = cls_max[cid * 6 + 4], mto = cls_max[cid * 6 + 5];
+    const u64 Mbw = magic[0], Mco = magic[2], Mfr = magic[3], Mpw = magic[4], Mto = magic[5];
     const u32 hm = meta_healthy(s.meta[n]);
     u32 out[G];
     bool big = false;
@@ -346,7 +381,8 @@ __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__r
         u32 cs = 0;
         if (bw <= mbw && ck <= mck && co <= mco && pw <= mpw && fr <= mfr && to <= mto) {
             bool b = false;
-            cs = div100(bw, mbw, b) + div100(ck, mbw, b) + div100(co, mco, b) + div100(pw, mpw, b) + div100(fr, mfr, b) * 2u + div100(to, mto, b);
+            cs = div100(bw, mbw, Mbw, b) + div100(ck, mbw, Mbw, b) + div100(co, mco, Mco, b) + div100(pw, mpw, Mpw, b) +
+                 div100(fr, mfr, Mfr, b) * 2u + div100(to, mto, Mto, b);
             b |= cs >= CS_LIMIT;
             big |= b;
             cs &= CS_SCORE_MASK;
@@ -375,11 +411,6 @@ struct NodeRegs {
     bool ok[NPL];     // node exists and has an SCV
     bool clkok[NPL];  // enough healthy cards with Clock == c for the current group (true without scv/clock)
 };
-
-__device__ __forceinline__ void load8(const u32 *p, u32 *dst) {
-    const uint4 a = reinterpret_cast<const uint4 *>(p)[0], b = reinterpret_cast<const uint4 *>(p)[1];
-    dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; dst[3] = a.w; dst[4] = b.x; dst[5] = b.y; dst[6] = b.z; dst[7] = b.w;
-}
 
 template <int NPL>
 __device__ __forceinline__ void hot_load_nodes(NodeRegs<NPL> &r, const DevSnap &s, u32 base, u32 lane) {

@@ -600,7 +600,7 @@ static int fast_phase0(yoda_ctx *c) {
     CU(cudaEventRecord(c->ev[EV_PREP], st));
     CU(cudaMemsetAsync(c->fw_step, 0, (size_t)P * 6 * sizeof(u32), st));
     if (N) {
-        dim3 grid((N + MAXT - 1) / MAXT, c->fw_n_groups);
+        const dim3 grid((N + MAXT - 1) / MAXT, std::max(1u, std::min(32u, (c->fw_n_groups + MAXG_TILE - 1) / MAXG_TILE)));
         k_max_thresholds<<<grid, MAXT, 0, st>>>(c->snap, c->fw_gdesc, c->fw_n_groups, c->fw_m_sorted, c->fw_step, P);
         LAUNCHED(c);
     }
