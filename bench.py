@@ -99,6 +99,8 @@ class ClockSampler:
 def workload(args, rank, world):
     from yoda_scheduler_b200 import synth
     n_nodes, n_pods, pod_seed = synth.CONFIGS[args.config]
+    if args.config == "c4":
+        n_nodes //= world   # config 4 is ONE 1M-node cluster node-sharded over the GPUs (strong scaling)
     if args.nodes:
         n_nodes = args.nodes
     if args.pods:
@@ -317,7 +319,7 @@ def main():
         step_bytes = algorithmic_bytes(n_pods, n_nodes) if full else n_nodes * R_NODE + n_pods * (R_POD + R_OUT)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64" if t_last.path == 0 else "u32",
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if args.config == "c4" else "weak", "vs_baseline": None, "dtype": "u64" if t_last.path == 0 else "u32",
             "data": "synthetic",
             "config": {"workload": f"{args.config}: {n_nodes} nodes x 8 cards per GPU ({total_nodes} total, node-sharded), {n_pods} pods, mode={args.mode}",
                        "l2": "every step writes the result matrices (>> 126 MB L2), which sweeps L2 between iterations; the snapshot is L2-resident by design",

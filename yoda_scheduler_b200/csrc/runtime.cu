@@ -147,7 +147,7 @@ struct yoda_ctx {
 };
 
 #define FAST_CLASS_CAP 4096u
-#define FAST_TABLE_BYTES (1ull << 30)
+#define FAST_TABLE_BYTES (8ull << 30)  // class tables: 32 B per node per class; more classes than fit -> direct path
 
 struct DeviceGuard {
     int prev = -1;
