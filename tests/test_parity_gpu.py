@@ -286,3 +286,50 @@ def test_config_c4_shape_sharded_on_one_gpu():
         c.phase_run(3)
         assert np.array_equal(c.phase_finish(), want)
         c.close()
+
+
+def test_fallback_when_groups_exceed_capacity():
+    """More than 4096 requirement groups in one batch: the fast path hands the batch to the exact
+    direct kernels (decided after grouping).  Results must not care."""
+    snap = synth.make_snapshot(257)
+    snap.card_number[:] = np.arange(257, dtype=np.uint64) * 40          # spread CardNumber so that number matters
+    labels = [{"scv/number": str(i)} for i in range(6000)]               # 6000 distinct groups (number only)
+    reqs = pods_to_requests(labels)
+    res, mats, t = gpu_cycle(snap, reqs, api.EVAL_FULL)
+    assert t.path == 0
+    assert_matches_oracle(snap, labels, res, mats)
+
+
+def test_fallback_when_classes_exceed_capacity():
+    """More distinct maxima tuples than class tables: fast maxima phase, then the direct kernels for
+    scoring (the switch happens between phases and must be seamless)."""
+    n_nodes = 700
+    nodes = []
+    for i in range(n_nodes):
+        cards = [{"health": "Healthy", "free": 8 * i + g + 1, "total": 1_000_000 - (8 * i + g), "clock": 1000, "core": 10, "bandwidth": 10, "power": 10}
+                 for g in range(8)]
+        nodes.append({"name": f"n{i}", "has_scv": True, "card_number": 8, "cards": cards, "free_sum": sum(c["free"] for c in cards),
+                      "total_sum": sum(c["total"] for c in cards), "pods": []})
+    snap = Snapshot.from_nodes(nodes)
+    labels = [{"scv/memory": str(m)} for m in range(1, 5201)]             # MaxTotalMemory differs for every pod
+    reqs = pods_to_requests(labels)
+    res, mats, t = gpu_cycle(snap, reqs, api.EVAL_FULL)
+    assert t.path == 0 and len(np.unique(res["max_total_memory"])) > 4096
+    assert_matches_oracle(snap, labels, res, mats)
+    # a batch that fits the tables takes the fast path on the same snapshot
+    res2, mats2, t2 = gpu_cycle(snap, reqs[:500], api.EVAL_FULL)
+    assert t2.path == 1
+    assert_matches_oracle(snap, labels[:500], res2, mats2)
+
+
+def test_fast_path_is_the_one_that_runs():
+    """Guard against a silent fallback: the synthetic configs must use the narrow fast path."""
+    snap = synth.make_snapshot(5000)
+    reqs = synth.make_requests(1000, synth.SEED + 2)
+    with api.Context(5000) as ctx:
+        ctx.load_snapshot(snap)
+        ctx.eval(reqs, api.EVAL_FULL)
+        t = ctx.timing()
+        assert t.path == 1 and t.n_groups > 10 and t.n_classes > 5 and t.kernels > 10
+        ctx.eval(reqs, api.EVAL_FULL | api.EVAL_FORCE_DIRECT)
+        assert ctx.timing().path == 0

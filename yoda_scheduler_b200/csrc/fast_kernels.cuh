@@ -45,7 +45,7 @@ struct GroupDesc {
 
 // counters shared between the grouping kernels and the host
 struct FastCtl {
-    u32 n_groups, n_classes, p0 /* first sorted position with scv/clock present */, err;
+    u32 n_groups, n_classes, reserved, err;
 };
 
 __device__ __forceinline__ u32 clamp32(u64 v) { return v > 0xFFFFFFFFull ? 0xFFFFFFFFu : (u32)v; }
@@ -118,14 +118,13 @@ __global__ void k_group_insert(const PodC *__restrict__ pods, u32 P, u64 *gkeys,
 // pod -> gid, sort key (has-clock | gid | memory), group descriptor
 __global__ void k_group_assign(const PodC *__restrict__ pods, u32 P, const u32 *__restrict__ slot_of_pod,
                                const u32 *__restrict__ gids, GroupDesc *gdesc, u32 gcap, u64 *sort_keys, u32 *sort_vals,
-                               u32 *pod_gid, FastCtl *ctl) {
+                               FastCtl *ctl) {
     u32 p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     const PodC pod = pods[p];
     u32 n32, c32, gf;
     group_key(pod, n32, c32, gf);
     const u32 gid = gids[slot_of_pod[p]];
-    pod_gid[p] = gid;
     const u32 m32 = clamp32(pod.mem);
     sort_keys[p] = ((u64)(gf & YODA_POD_HAS_CLOCK ? 1 : 0) << (32 + FAST_GID_BITS)) | ((u64)(gid & (FAST_GROUP_CAP - 1)) << 32) | m32;
     sort_vals[p] = p;
@@ -139,10 +138,9 @@ __global__ void k_group_assign(const PodC *__restrict__ pods, u32 P, const u32 *
     }
 }
 
-// sorted pod records + group segment bounds + first clock position
+// sorted pod records + group segment bounds
 __global__ void k_build_sorted(const PodC *__restrict__ pods, u32 P, const u64 *__restrict__ keys_sorted,
-                               const u32 *__restrict__ vals_sorted, GroupDesc *gdesc, u32 gcap, PodS *out, u32 *m_sorted,
-                               FastCtl *ctl) {
+                               const u32 *__restrict__ vals_sorted, GroupDesc *gdesc, u32 gcap, PodS *out, u32 *m_sorted) {
     u32 i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P) return;
     const u64 key = keys_sorted[i];
@@ -169,7 +167,6 @@ __global__ void k_build_sorted(const PodC *__restrict__ pods, u32 P, const u64 *
         if (head) gdesc[gid].seg_start = i;
         if (tail) gdesc[gid].seg_end = i + 1;
     }
-    if (head && ((key >> (32 + FAST_GID_BITS)) & 1ull)) atomicMin(&ctl->p0, i);
 }
 
 // ------------------------------------------------------------------------------------------

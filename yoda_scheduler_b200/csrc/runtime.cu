@@ -133,7 +133,7 @@ struct yoda_ctx {
     int ph_path = 0;  // path of the evaluation in flight: 0 direct, 1 fast
     u32 fw_pods_cap = 0, fw_htab = 0;
     u64 *fw_gkeys = nullptr, *fw_ckeys = nullptr;
-    u32 *fw_gids = nullptr, *fw_cids = nullptr, *fw_crep = nullptr, *fw_slot = nullptr, *fw_pod_gid = nullptr;
+    u32 *fw_gids = nullptr, *fw_cids = nullptr, *fw_crep = nullptr, *fw_slot = nullptr;
     u64 *fw_keys_in = nullptr, *fw_keys_out = nullptr;
     u32 *fw_vals_in = nullptr, *fw_vals_out = nullptr;
     void *fw_cub_tmp = nullptr;
@@ -265,7 +265,7 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     dev_free(c->d_hilo); dev_free(c->d_ckey); dev_free(c->d_res);
     dev_free(c->d_raw); dev_free(c->d_norm); dev_free(c->d_bits);
     dev_free(c->fw_gkeys); dev_free(c->fw_ckeys); dev_free(c->fw_gids); dev_free(c->fw_cids); dev_free(c->fw_crep);
-    dev_free(c->fw_slot); dev_free(c->fw_pod_gid); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
+    dev_free(c->fw_slot); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
     dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_gdesc); dev_free(c->fw_pods);
     dev_free(c->fw_m_sorted); dev_free(c->fw_step); dev_free(c->fw_cls_max); dev_free(c->fw_tables); dev_free(c->fw_ctl);
     if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
@@ -492,7 +492,7 @@ static int ensure_fast(yoda_ctx *c, u32 P) {
     u32 htab = 1024;
     while (htab < 2 * cap) htab <<= 1;
     dev_free(c->fw_gkeys); dev_free(c->fw_ckeys); dev_free(c->fw_gids); dev_free(c->fw_cids); dev_free(c->fw_crep);
-    dev_free(c->fw_slot); dev_free(c->fw_pod_gid); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
+    dev_free(c->fw_slot); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
     dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_pods);
     dev_free(c->fw_m_sorted); dev_free(c->fw_step);
     if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
@@ -504,7 +504,6 @@ static int ensure_fast(yoda_ctx *c, u32 P) {
     TRY(dev_alloc(&c->fw_cids, htab));
     TRY(dev_alloc(&c->fw_crep, htab));
     TRY(dev_alloc(&c->fw_slot, cap));
-    TRY(dev_alloc(&c->fw_pod_gid, cap));
     TRY(dev_alloc(&c->fw_keys_in, cap));
     TRY(dev_alloc(&c->fw_keys_out, cap));
     TRY(dev_alloc(&c->fw_vals_in, cap));
@@ -572,7 +571,7 @@ static int fast_phase0(yoda_ctx *c) {
     const u32 P = c->ph_P, N = c->snap.n_nodes;
     cudaStream_t st = c->stream;
     const u32 pb = (P + 255) / 256;
-    const FastCtl init = {0, 0, P, 0};
+    const FastCtl init = {0, 0, 0, 0};
     *c->fw_hctl = init;
     CU(cudaMemcpyAsync(c->fw_ctl, c->fw_hctl, sizeof(FastCtl), cudaMemcpyHostToDevice, st));
     k_hash_clear<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_gkeys, c->fw_gids, c->fw_htab);
@@ -588,14 +587,14 @@ static int fast_phase0(yoda_ctx *c) {
         return YODA_OK;
     }
     k_group_assign<<<pb, 256, 0, st>>>(c->d_pods, P, c->fw_slot, c->fw_gids, c->fw_gdesc, FAST_GROUP_CAP, c->fw_keys_in, c->fw_vals_in,
-                                       c->fw_pod_gid, c->fw_ctl);
+                                       c->fw_ctl);
     LAUNCHED(c);
     size_t bytes = c->fw_cub_bytes;
     CU(cub::DeviceRadixSort::SortPairs(c->fw_cub_tmp, bytes, c->fw_keys_in, c->fw_keys_out, c->fw_vals_in, c->fw_vals_out, (int)P, 0,
                                        33 + FAST_GID_BITS, st));
     c->launches += 6;  // cub radix sort passes (library kernels)
     k_build_sorted<<<pb, 256, 0, st>>>(c->d_pods, P, c->fw_keys_out, c->fw_vals_out, c->fw_gdesc, FAST_GROUP_CAP, c->fw_pods,
-                                       c->fw_m_sorted, c->fw_ctl);
+                                       c->fw_m_sorted);
     LAUNCHED(c);
     CU(cudaEventRecord(c->ev[EV_PREP], st));
     CU(cudaMemsetAsync(c->fw_step, 0, (size_t)P * 6 * sizeof(u32), st));
@@ -720,6 +719,7 @@ static int phase3(yoda_ctx *c) {
 static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
     if (c->flushed_uncommitted || c->n_upd)
         return fail(YODA_E_STATE, "uncommitted node updates are pending: call yoda_commit before evaluating");
+    if (P > (1u << 22)) return fail(YODA_E_RANGE, "batch of %u pods exceeds the limit of %u per call; split it", P, 1u << 22);
     TRY(ensure_pods(c, P));
     c->stride = round_up(std::max(c->snap.n_nodes, 1u), 1024);  // rows padded to the hot kernels' CTA tile
     if (flags & YODA_EVAL_FULL) TRY(ensure_matrices(c, P, c->stride));
