@@ -333,3 +333,19 @@ def test_fast_path_is_the_one_that_runs():
         assert t.path == 1 and t.n_groups > 10 and t.n_classes > 5 and t.kernels > 10
         ctx.eval(reqs, api.EVAL_FULL | api.EVAL_FORCE_DIRECT)
         assert ctx.timing().path == 0
+
+
+@pytest.mark.parametrize("n_pods", [1, 5, 40])
+def test_class_table_overflow_falls_back(n_pods):
+    """A narrow snapshot whose card scores do not fit the packed class table (Clock*100/MaxBandwidth is
+    unbounded, algorithm.go:60): the fast path notices while building the tables -- at the end of the
+    evaluation for small batches, before scoring otherwise -- and the exact kernels take over."""
+    nodes = [{"name": f"n{i}", "has_scv": True, "card_number": 2, "free_sum": 5000, "total_sum": 16000, "pods": [],
+              "cards": [{"health": "Healthy", "free": 4000 + i, "total": 8000, "clock": 30_000_000 + i, "core": 100, "bandwidth": 1 + (i % 3), "power": 50},
+                        {"health": "Healthy", "free": 1000, "total": 8000, "clock": 1000, "core": 100, "bandwidth": 2, "power": 50}]}
+             for i in range(70)]
+    snap = Snapshot.from_nodes(nodes)
+    labels = [{"scv/memory": str(500 + 37 * k)} for k in range(n_pods)]
+    res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_FULL)
+    assert t.path == 0
+    assert_matches_oracle(snap, labels, res, mats)

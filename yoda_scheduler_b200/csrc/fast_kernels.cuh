@@ -138,6 +138,37 @@ __global__ void k_group_assign(const PodC *__restrict__ pods, u32 P, const u32 *
     }
 }
 
+// Small batches (<= FAST_SMALL_P pods, the one-pod-at-a-time scheduling cycle): every pod is its own
+// group and its own class, so hashing, sorting and the host round trips that size their grids are
+// skipped altogether.
+#define FAST_SMALL_P 8
+__global__ void k_small_groups(const PodC *__restrict__ pods, u32 P, GroupDesc *gdesc, PodS *out, u32 *m_sorted) {
+    const u32 p = threadIdx.x;
+    if (p >= P) return;
+    const PodC pod = pods[p];
+    u32 n32, c32, gf;
+    group_key(pod, n32, c32, gf);
+    GroupDesc g;
+    g.flags = gf; g.c = c32; g.num = n32; g.seg_start = p; g.seg_end = p + 1; g.pad0 = g.pad1 = g.pad2 = 0;
+    gdesc[p] = g;
+    PodS s;
+    s.m = clamp32(pod.mem);
+    s.c = (pod.flags & YODA_POD_HAS_CLOCK) ? clamp32(pod.clk) : 0u;
+    s.num = clamp32(pod.num);
+    const u32 req = min(s.num, 255u);
+    s.req = ((pod.flags & YODA_POD_HAS_MEMORY) ? req : 0u) | (((pod.flags & YODA_POD_HAS_CLOCK) ? req : 0u) << 8) | (pod.flags << 16);
+    s.cls = p; s.orig = p; s.gid = p; s.pad = 0;
+    out[p] = s;
+    m_sorted[p] = s.m;
+}
+__global__ void k_small_classes(u32 P, const u64 *__restrict__ max6, u32 *cls_max, FastCtl *ctl) {
+    const u32 t = threadIdx.x;
+    if (t >= P * 6) return;
+    const u64 v = max6[t];
+    if (v > 0xFFFFFFFFull) atomicOr(&ctl->err, FAST_ERR_WIDE_CLASS);  // another shard may be wide
+    cls_max[t] = (u32)v;
+}
+
 // sorted pod records + group segment bounds
 __global__ void k_build_sorted(const PodC *__restrict__ pods, u32 P, const u64 *__restrict__ keys_sorted,
                                const u32 *__restrict__ vals_sorted, GroupDesc *gdesc, u32 gcap, PodS *out, u32 *m_sorted) {

@@ -144,6 +144,7 @@ struct yoda_ctx {
     u32 fw_tables_classes = 0;
     FastCtl *fw_ctl = nullptr, *fw_hctl = nullptr;
     u32 fw_n_groups = 0, fw_n_classes = 0;
+    bool fw_small = false, fw_allow_defer = false, fw_deferred_err = false;
 };
 
 #define FAST_CLASS_CAP 4096u
@@ -571,9 +572,22 @@ static int fast_phase0(yoda_ctx *c) {
     const u32 P = c->ph_P, N = c->snap.n_nodes;
     cudaStream_t st = c->stream;
     const u32 pb = (P + 255) / 256;
-    const FastCtl init = {0, 0, 0, 0};
-    *c->fw_hctl = init;
-    CU(cudaMemcpyAsync(c->fw_ctl, c->fw_hctl, sizeof(FastCtl), cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(c->fw_ctl, 0, sizeof(FastCtl), st));
+    c->fw_small = P <= FAST_SMALL_P && P <= fast_class_cap(c);
+    if (c->fw_small) {  // one pod = one group = one class: no hashing, no sort, no host round trip
+        k_small_groups<<<1, 32, 0, st>>>(c->d_pods, P, c->fw_gdesc, c->fw_pods, c->fw_m_sorted);
+        LAUNCHED(c);
+        c->fw_n_groups = P;
+        CU(cudaEventRecord(c->ev[EV_PREP], st));
+        CU(cudaMemsetAsync(c->fw_step, 0, (size_t)P * 6 * sizeof(u32), st));
+        if (N) {
+            k_max_thresholds<<<dim3((N + MAXT - 1) / MAXT, 1), MAXT, 0, st>>>(c->snap, c->fw_gdesc, P, c->fw_m_sorted, c->fw_step, P);
+            LAUNCHED(c);
+        }
+        k_max_scan<<<dim3(P, 6), SCANT, 0, st>>>(c->fw_gdesc, P, c->fw_step, c->fw_pods, c->d_max6, P);
+        LAUNCHED(c);
+        return YODA_OK;
+    }
     k_hash_clear<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_gkeys, c->fw_gids, c->fw_htab);
     LAUNCHED(c);
     k_group_insert<<<pb, 256, 0, st>>>(c->d_pods, P, c->fw_gkeys, c->fw_htab - 1, c->fw_slot);
@@ -639,6 +653,30 @@ static int fast_classes(yoda_ctx *c) {
     cudaStream_t st = c->stream;
     const u32 pb = (P + 255) / 256;
     const u32 ccap = fast_class_cap(c);
+    if (c->fw_small) {
+        k_small_classes<<<1, 64, 0, st>>>(P, c->d_max6, c->fw_cls_max, c->fw_ctl);
+        LAUNCHED(c);
+        c->fw_n_classes = P;
+        if (c->fw_n_classes > c->fw_tables_classes) {
+            CU(cudaStreamSynchronize(st));
+            dev_free(c->fw_tables);
+            c->fw_tables_classes = 0;
+            const u32 want = std::min(ccap, 64u);
+            TRY(dev_alloc(&c->fw_tables, (size_t)want * c->snap.cap * G));
+            c->fw_tables_classes = want;
+        }
+        if (N) {
+            k_class_tables<<<dim3((N + CLST - 1) / CLST, P), CLST, 0, st>>>(c->snap, c->fw_cls_max, P, c->fw_tables, c->fw_ctl);
+            LAUNCHED(c);
+        }
+        if (c->fw_allow_defer) {
+            c->fw_deferred_err = true;  // checked once at the end of the evaluation instead of stalling here
+            return YODA_OK;
+        }
+        TRY(fast_read_ctl(c));
+        if (c->fw_hctl->err) c->ph_path = 0;
+        return YODA_OK;
+    }
     k_hash_clear<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_ckeys, c->fw_crep, c->fw_htab);
     LAUNCHED(c);
     k_class_insert<<<pb, 256, 0, st>>>(c->fw_pods, P, c->d_max6, c->fw_ckeys, c->fw_htab - 1, c->fw_crep, c->fw_slot);
@@ -769,6 +807,8 @@ static void collect_timing(yoda_ctx *c, bool copies) {
 }
 
 static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
+    c->fw_allow_defer = (c->comm == nullptr);
+    c->fw_deferred_err = false;
     TRY(phase0(c, d_req));
     TRY(exchange_locked(c, 0));
     TRY(phase1(c));
@@ -776,12 +816,27 @@ static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
     TRY(phase2(c));
     TRY(exchange_locked(c, 2));
     TRY(phase3(c));
+    c->fw_allow_defer = false;
     c->ph_done = 3;
     c->last_P = c->ph_P;
     c->last_full = (c->ph_flags & YODA_EVAL_FULL) != 0;
     return YODA_OK;
 }
 
+// Small-batch path: the "every class fits the packed table" verdict was left on the device; `err` is
+// its value.  If it failed, redo the batch with the exact kernels.
+static int redo_direct_if_flagged(yoda_ctx *c, const yoda_pod_req *d_req, u32 err) {
+    c->fw_deferred_err = false;
+    if (!err) return YODA_OK;
+    c->ph_path = 0;
+    TRY(phase0(c, d_req));
+    TRY(phase1(c));
+    TRY(phase2(c));
+    TRY(phase3(c));
+    return YODA_OK;
+}
+
+#define STAGE_PODS 4096u  // batches up to this size go through the library's pinned staging buffers
 extern "C" int yoda_eval_batch(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32 flags, yoda_pod_result *out) {
     if (!c || (P && (!pods || !out))) return fail(YODA_E_ARG, "null argument");
     std::lock_guard<std::mutex> lk(c->mu);
@@ -789,14 +844,26 @@ extern "C" int yoda_eval_batch(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32
     if (P == 0) return YODA_OK;
     TRY(begin_locked(c, P, flags));
     cudaStream_t st = c->stream;
+    const bool staged = P <= STAGE_PODS;  // small batches: one cheap host copy buys truly asynchronous DMA
+    if (staged) memcpy(c->h_req, pods, (size_t)P * sizeof(yoda_pod_req));
     CU(cudaEventRecord(c->ev[EV_H2D0], st));
-    CU(cudaMemcpyAsync(c->d_req, pods, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(c->d_req, staged ? c->h_req : pods, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, st));
     CU(cudaEventRecord(c->ev[EV_H2D1], st));
     TRY(run_all_locked(c, c->d_req));
+    yoda_pod_result *dst = staged ? c->h_res : out;
     CU(cudaEventRecord(c->ev[EV_D2H0], st));
-    CU(cudaMemcpyAsync(out, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
     CU(cudaEventRecord(c->ev[EV_D2H1], st));
+    const bool deferred = c->fw_deferred_err;
+    if (deferred) CU(cudaMemcpyAsync(c->fw_hctl, c->fw_ctl, sizeof(FastCtl), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    if (deferred && c->fw_hctl->err) {
+        TRY(redo_direct_if_flagged(c, c->d_req, c->fw_hctl->err));
+        CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    c->fw_deferred_err = false;
+    if (staged) memcpy(out, c->h_res, (size_t)P * sizeof(yoda_pod_result));
     collect_timing(c, true);
     return YODA_OK;
 }
@@ -808,6 +875,10 @@ extern "C" int yoda_eval_batch_device(yoda_ctx *c, const void *d_pods, u32 P, u3
     if (P == 0) return YODA_OK;
     TRY(begin_locked(c, P, flags));
     TRY(run_all_locked(c, (const yoda_pod_req *)d_pods));
+    if (c->fw_deferred_err) {
+        TRY(fast_read_ctl(c));
+        TRY(redo_direct_if_flagged(c, (const yoda_pod_req *)d_pods, c->fw_hctl->err));
+    }
     if (d_out)
         CU(cudaMemcpyAsync(d_out, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToDevice, c->stream));
     return YODA_OK;
@@ -873,6 +944,8 @@ extern "C" int yoda_phase_begin(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u3
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard dg(c->cfg.device);
     TRY(begin_locked(c, P, flags));
+    c->fw_allow_defer = false;
+    c->fw_deferred_err = false;
     CU(cudaMemcpyAsync(c->d_req, pods, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));  // caller's buffer may be pageable and is not retained
     return YODA_OK;
