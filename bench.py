@@ -337,6 +337,22 @@ def main():
         if churn:
             line["churn"] = {"nodes_updated_per_tick": int(n_touch), "upsert_commit_ms_per_tick": tick_ms[0] / max(tick_ms[1], 1),
                              "bytes_per_tick": int(n_touch * 432), "note": "tick (pinned ring -> async H2D -> scatter + derive kernels -> epoch) is inside every timed step"}
+        if world == 1 and args.mode == "full" and not args.no_latency:
+            # the same batch in DECIDE mode (per-pod results only: no matrices, one fused score+choice pass)
+            dflags = api.EVAL_DECIDE | (api.EVAL_FORCE_DIRECT if args.force_direct else 0)
+            for _ in range(3):
+                ctx.eval_device(d_reqs.data_ptr(), n_pods, dflags)
+            ctx.sync()
+            d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with torch.cuda.stream(stream):
+                d0.record(stream)
+                for _ in range(10):
+                    ctx.eval_device(d_reqs.data_ptr(), n_pods, dflags)
+                d1.record(stream)
+            torch.cuda.synchronize()
+            dms = d0.elapsed_time(d1) / 10
+            line["decide_mode"] = {"ms_per_step": dms, "value": evals / (dms * 1e-3), "unit": UNIT,
+                                   "note": "YODA_EVAL_DECIDE: maxima, lowest/highest, feasible count and chosen node per pod; no matrices"}
         if world == 1 and not args.no_latency:
             # p50/p99 batch latency at this snapshot size, host buffers in -> per-pod results out
             lat = {}

@@ -109,11 +109,12 @@ def test_empty_and_degenerate():
         assert r["chosen"][0] == -1 and r["max_core"][0] == 1
 
 
-def test_incremental_upserts_equal_full_rebuild():
-    """Churn (BASELINE config 5 shape, small): 10% of the nodes change per tick; the incrementally
-    maintained device snapshot must answer exactly like one rebuilt from scratch."""
+@pytest.mark.parametrize("N,P", [(3000, 300), (50000, 384)])
+def test_incremental_upserts_equal_full_rebuild(N, P):
+    """Churn (BASELINE config 5: 50k nodes, 10% of them updated per tick, interleaved with scheduling
+    cycles; also a small shape): the incrementally maintained device snapshot must answer exactly like
+    one rebuilt from scratch, and like the oracle."""
     rng = np.random.default_rng(5)
-    N, P = 3000, 300
     snap = synth.make_snapshot(N)
     reqs = synth.make_requests(P, synth.SEED + 5)
     labels = synth.make_pod_labels(P, synth.SEED + 5)

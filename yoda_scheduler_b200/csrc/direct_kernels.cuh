@@ -333,8 +333,9 @@ __global__ void __launch_bounds__(DCT) k_direct_out(DevSnap s, const PodC *__res
 }
 
 // Assemble yoda_pod_result from the (already cross-shard reduced) partial buffers.
+// packed_key: ckey holds (top score << 32 | ~global index) instead of 2^32 - global index (merged DECIDE pass)
 __global__ void k_finalize(const u64 *__restrict__ max6, const u64 *__restrict__ count, const u64 *__restrict__ hilo,
-                           const u64 *__restrict__ ckey, yoda_pod_result *__restrict__ out, u32 P) {
+                           const u64 *__restrict__ ckey, yoda_pod_result *__restrict__ out, u32 P, bool packed_key) {
     u32 p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     yoda_pod_result r;
@@ -349,7 +350,7 @@ __global__ void k_finalize(const u64 *__restrict__ max6, const u64 *__restrict__
     r.lowest = lo;
     r.highest = hi;
     r.feasible = (u32)count[p];
-    r.chosen = ckey_to_idx(ckey[p]);
+    r.chosen = packed_key ? (count[p] ? (i32)(0xFFFFFFFFu - (u32)ckey[p]) : -1) : ckey_to_idx(ckey[p]);
     out[p] = r;
 }
 

@@ -567,16 +567,21 @@ struct ScoreSmem {
     uint4 blk[HOT_CHUNK / SCORE_BLK];  // gid (or ~0 if mixed), cls, first m, last m of four consecutive pods
     __align__(16) u32 hi_s[HOT_WARPS][HOT_CHUNK];
     __align__(16) u32 lo_s[HOT_WARPS][HOT_CHUNK];
+    __align__(16) u32 cnt_s[HOT_WARPS][HOT_CHUNK];   // DECIDE only: feasible nodes of the warp's slots
+    __align__(16) u32 best_s[HOT_WARPS][HOT_CHUNK];  // DECIDE only: lowest node index holding the warp's top score
 };
 
 // score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145).
 // Pods are taken four at a time: a per-chunk summary says whether the four share group and class
 // with ascending memory values; if so and no lane's validity bound is crossed by the largest of
 // the four, all four inherit the warp's current (highest, lowest) with one test.
-template <int NPL>
+// DECIDE (per-pod results only, one GPU): the same pass also counts the feasible nodes and tracks the
+// lowest-index node holding the top score, packed as (score << 32 | ~index) so that one 64-bit
+// atomicMax across the node tiles yields the choice -- no output pass is needed at all.
+template <int NPL, bool DECIDE>
 __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u32 tile, u32 chunk, const DevSnap &s,
                                            const PodS *__restrict__ pods, u32 p_begin, u32 p_end, const u32 *__restrict__ tables,
-                                           u64 *hilo) {
+                                           u64 *hilo, u64 *count, u64 *dkey) {
     const u32 lane = tid & 31, warp = tid >> 5;
     const u32 c0 = p_begin + chunk * HOT_CHUNK;
     const u32 cn = min(HOT_CHUNK, p_end - c0);
@@ -617,6 +622,7 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
 #pragma unroll
     for (int j = 0; j < NPL; ++j) { hi_l[j] = 0; lo_l[j] = 0xFFFFFFFFu; bound[j] = 0; }
     u32 hi_w = 0, lo_w = 0xFFFFFFFFu, bmin = 0;  // bmin = min over the lane's slots of bound[j]
+    u32 cnt_w = 0, best_w = 0xFFFFFFFFu;
     for (u32 i0 = 0; i0 < cn; i0 += SCORE_BLK) {
         const uint4 bs = sm.blk[i0 / SCORE_BLK];
         if (bs.x == cur_gid && bs.y == cur_cls && bs.z >= cur_m && !__any_sync(0xFFFFFFFFu, bs.w > bmin)) {
@@ -624,6 +630,10 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
             if (lane == 0) {
                 *reinterpret_cast<uint4 *>(&sm.hi_s[warp][i0]) = make_uint4(hi_w, hi_w, hi_w, hi_w);
                 *reinterpret_cast<uint4 *>(&sm.lo_s[warp][i0]) = make_uint4(lo_w, lo_w, lo_w, lo_w);
+                if (DECIDE) {
+                    *reinterpret_cast<uint4 *>(&sm.cnt_s[warp][i0]) = make_uint4(cnt_w, cnt_w, cnt_w, cnt_w);
+                    *reinterpret_cast<uint4 *>(&sm.best_s[warp][i0]) = make_uint4(best_w, best_w, best_w, best_w);
+                }
             }
             continue;
         }
@@ -651,11 +661,25 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
                 for (int j = 1; j < NPL; ++j) { hi = max(hi, hi_l[j]); lo = min(lo, lo_l[j]); bmin = min(bmin, bound[j]); }
                 hi_w = __reduce_max_sync(0xFFFFFFFFu, hi);
                 lo_w = __reduce_min_sync(0xFFFFFFFFu, lo);
+                if (DECIDE) {
+                    cnt_w = 0; best_w = 0xFFFFFFFFu;
+#pragma unroll
+                    for (int j = NPL - 1; j >= 0; --j) {
+                        const bool fitj = lo_l[j] != 0xFFFFFFFFu;
+                        cnt_w += __popc(__ballot_sync(0xFFFFFFFFu, fitj));
+                        const u32 top = __ballot_sync(0xFFFFFFFFu, fitj && hi_l[j] == hi_w);
+                        if (top) best_w = base + j * 32 + (__ffs(top) - 1);
+                    }
+                }
             }
             cur_m = pod.m;
             if (lane == 0) {
                 sm.hi_s[warp][i] = hi_w;
                 sm.lo_s[warp][i] = lo_w;
+                if (DECIDE) {
+                    sm.cnt_s[warp][i] = cnt_w;
+                    sm.best_s[warp][i] = best_w;
+                }
             }
         }
     }
@@ -671,6 +695,16 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
             const u32 orig = sm.sp[2 * i + 1].y;
             atomicMax(&hilo[2 * (size_t)orig], (u64)hi);
             atomicMax(&hilo[2 * (size_t)orig + 1], ~(u64)lo);
+            if (DECIDE) {
+                u32 cnt = 0, best = 0xFFFFFFFFu;
+#pragma unroll
+                for (int w = HOT_WARPS - 1; w >= 0; --w) {  // warps hold ascending node ranges: the last match wins = lowest index
+                    cnt += sm.cnt_s[w][i];
+                    if (sm.cnt_s[w][i] && sm.hi_s[w][i] == hi) best = sm.best_s[w][i];
+                }
+                atomicAdd(&count[orig], (u64)cnt);
+                atomicMax(&dkey[orig], ((u64)hi << 32) | (u64)(0xFFFFFFFFu - (s.node_base + best)));
+            }
         }
     }
 }
@@ -806,11 +840,11 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
     }
 }
 
-template <int NPL>
+template <int NPL, bool DECIDE>
 __global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
-                                                               const u32 *__restrict__ tables, u64 *hilo) {
+                                                            const u32 *__restrict__ tables, u64 *hilo, u64 *count, u64 *dkey) {
     __shared__ ScoreSmem sm;
-    score_body<NPL>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo);
+    score_body<NPL, DECIDE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo, count, dkey);
 }
 
 template <int NPL, bool WRITE>

@@ -145,6 +145,7 @@ struct yoda_ctx {
     FastCtl *fw_ctl = nullptr, *fw_hctl = nullptr;
     u32 fw_n_groups = 0, fw_n_classes = 0;
     bool fw_small = false, fw_allow_defer = false, fw_deferred_err = false;
+    bool fw_decide_merged = false;  // DECIDE on one GPU: the score pass also yields counts and the node choice
 };
 
 #define FAST_CLASS_CAP 4096u
@@ -629,7 +630,12 @@ static dim3 hot_grid(const yoda_ctx *c, u32 n_pods) {
 
 static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
-    k_fast_score<4><<<hot_grid(c, p_end - p_begin), HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo);
+    if (c->fw_decide_merged)
+        k_fast_score<4, true><<<hot_grid(c, p_end - p_begin), HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables,
+                                                                                         c->d_hilo, c->d_count, c->d_ckey);
+    else
+        k_fast_score<4, false><<<hot_grid(c, p_end - p_begin), HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables,
+                                                                                          c->d_hilo, c->d_count, c->d_ckey);
     LAUNCHED(c);
     return YODA_OK;
 }
@@ -734,6 +740,7 @@ static int phase0(yoda_ctx *c, const yoda_pod_req *d_req) {
 // phase 1: local lowest/highest over feasible nodes
 static int phase1(yoda_ctx *c) {
     if (c->ph_path == 1) TRY(fast_classes(c));
+    if (c->ph_path == 0) c->fw_decide_merged = false;
     if (c->ph_path == 1) TRY(fast_score_launch(c, 0, c->ph_P));
     if (c->ph_path == 0) TRY(direct_pods_launch(c, 1));
     CU(cudaEventRecord(c->ev[EV_SCORE], c->stream));
@@ -742,13 +749,15 @@ static int phase1(yoda_ctx *c) {
 
 // phase 2: output pass (matrices when FULL), feasible counts, node choice
 static int phase2(yoda_ctx *c) {
+    if (c->ph_path == 1 && c->fw_decide_merged) return YODA_OK;  // phase 1 already produced counts and choices
     if (c->ph_path == 1) return fast_out_launch(c, 0, c->ph_P);
     return direct_out_launch(c);
 }
 
 static int phase3(yoda_ctx *c) {
     const u32 P = c->ph_P;
-    k_finalize<<<(P + 255) / 256, 256, 0, c->stream>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, c->d_res, P);
+    k_finalize<<<(P + 255) / 256, 256, 0, c->stream>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, c->d_res, P,
+                                                       c->ph_path == 1 && c->fw_decide_merged);
     LAUNCHED(c);
     CU(cudaEventRecord(c->ev[EV_WRITE], c->stream));
     return YODA_OK;
@@ -809,6 +818,7 @@ static void collect_timing(yoda_ctx *c, bool copies) {
 static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
     c->fw_allow_defer = (c->comm == nullptr);
     c->fw_deferred_err = false;
+    c->fw_decide_merged = (c->comm == nullptr) && !(c->ph_flags & YODA_EVAL_FULL) && c->ph_path == 1;
     TRY(phase0(c, d_req));
     TRY(exchange_locked(c, 0));
     TRY(phase1(c));
@@ -829,6 +839,7 @@ static int redo_direct_if_flagged(yoda_ctx *c, const yoda_pod_req *d_req, u32 er
     c->fw_deferred_err = false;
     if (!err) return YODA_OK;
     c->ph_path = 0;
+    c->fw_decide_merged = false;
     TRY(phase0(c, d_req));
     TRY(phase1(c));
     TRY(phase2(c));
@@ -946,6 +957,7 @@ extern "C" int yoda_phase_begin(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u3
     TRY(begin_locked(c, P, flags));
     c->fw_allow_defer = false;
     c->fw_deferred_err = false;
+    c->fw_decide_merged = false;
     CU(cudaMemcpyAsync(c->d_req, pods, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));  // caller's buffer may be pageable and is not retained
     return YODA_OK;
