@@ -150,6 +150,13 @@ int yoda_result_matrices(yoda_ctx *ctx, void **d_bits, void **d_raw, void **d_no
  * used when the framework's list is not Yoda's own feasible set (other plugins filtered too). */
 int yoda_normalize_scores(yoda_ctx *ctx, int64_t *scores, uint32_t n);
 
+/* QueueSort for a pending batch: sort.Less / sort.GetPodPriority (pkg/yoda/sort/sort.go:8-18, wired at
+ * scheduler.go:105-107) order pods by the scv/priority label, higher first.  Given the priorities
+ * (host parses the label: strconv.Atoi, value kept even on a range error, 0 without the label), writes
+ * the batch order: order[k] = index of the pod consumed k-th.  Pods of equal priority keep their
+ * arrival order (Less is false both ways for them). */
+int yoda_queue_order(yoda_ctx *ctx, const int64_t *priority, uint32_t n, uint32_t *order);
+
 /* No counterpart in the reference.  The same rescale for callers that may not allocate: no
  * context, no cudaMalloc/cudaFree, no host allocation -- the only scratch is a fixed 16 KiB array
  * inside the library image (resident on every GPU that loads the library, until exit), which

@@ -44,6 +44,9 @@ def lib():
         L.ora_filter.argtypes = [C.c_void_p, C.c_uint32, C.c_char_p, C.c_char_p, C.c_char_p]
         L.ora_node_static.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
         L.ora_score_with_max.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ora_pod_priority.restype = C.c_int64
+        L.ora_pod_priority.argtypes = [C.c_char_p]
+        L.ora_queue_order.argtypes = [C.c_uint32, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -62,6 +65,18 @@ def normalize_score(scores: Sequence[int]) -> list:
     if rc:
         raise IndexError("NormalizeScore on an empty list panics in the reference (scheduler.go:135)")
     return a.tolist()
+
+
+def pod_priority(label: Optional[str]) -> int:
+    return int(lib().ora_pod_priority(None if label is None else label.encode()))
+
+
+def queue_order(priority_labels: Sequence[Optional[str]]) -> np.ndarray:
+    """Stable batch order under sort.Less (sort.go:8-18)."""
+    arr = _cstr_array(list(priority_labels))
+    order = np.zeros(len(priority_labels), np.uint32)
+    lib().ora_queue_order(len(priority_labels), C.cast(arr, C.c_void_p), order.ctypes.data)
+    return order
 
 
 def _cstr_array(vals: Sequence[Optional[str]]):

@@ -655,3 +655,35 @@ int ora_score_with_max(const ora_cluster *cl, const char *number, const char *me
     labels_free(&pod);
     return rc;
 }
+
+/* sort.go:8-18: Less(a, b) = priority(a) > priority(b), priority = Atoi(label scv/priority) with the
+ * error dropped (0 when the label is absent).  order[] = stable insertion order under Less. */
+static int64_t pod_priority(const char *label) {
+    if (!label) return 0;
+    /* strconv.Atoi returns the clamped value together with a range error; GetPodPriority keeps the value */
+    size_t n = strlen(label), i = 0;
+    int neg = 0;
+    if (n == 0) return 0;
+    if (label[0] == '+' || label[0] == '-') { neg = label[0] == '-'; i = 1; if (n == 1) return 0; }
+    unsigned __int128 acc = 0;
+    int over = 0;
+    for (; i < n; ++i) {
+        unsigned d = (unsigned char)label[i] - (unsigned)'0';
+        if (d > 9) return 0; /* syntax error -> 0 */
+        if (!over) { acc = acc * 10 + d; if (acc > ((unsigned __int128)1 << 63)) over = 1; }
+    }
+    if (!neg && acc > (((unsigned __int128)1 << 63) - 1)) over = 1;
+    if (over) return neg ? INT64_MIN : INT64_MAX;
+    return neg ? (int64_t)(0 - (uint64_t)acc) : (int64_t)(uint64_t)acc;
+}
+int64_t ora_pod_priority(const char *label) { return pod_priority(label); }
+void ora_queue_order(uint32_t n, const char *const *priority_labels, uint32_t *order) {
+    int64_t *pri = (int64_t *)malloc(sizeof(int64_t) * (n ? n : 1));
+    for (uint32_t i = 0; i < n; ++i) pri[i] = pod_priority(priority_labels[i]);
+    for (uint32_t i = 0; i < n; ++i) { /* insertion sort: move i before every earlier pod it is Less-than */
+        uint32_t k = i;
+        while (k > 0 && pri[i] > pri[order[k - 1]]) { order[k] = order[k - 1]; --k; }
+        order[k] = i;
+    }
+    free(pri);
+}

@@ -127,6 +127,13 @@ class Context:
         check(self.L.yoda_normalize_scores(self.h, a.ctypes.data, len(a)))
         return a
 
+    def queue_order(self, priorities) -> np.ndarray:
+        """Batch consumption order under sort.Less (scv/priority, higher first, stable)."""
+        pri = np.ascontiguousarray(priorities, dtype=np.int64)
+        order = np.zeros(len(pri), np.uint32)
+        check(self.L.yoda_queue_order(self.h, pri.ctypes.data, len(pri), order.ctypes.data))
+        return order
+
     # ---- phase-split evaluation (host-driven exchange between node shards) ---------------
     def phase_begin(self, reqs: np.ndarray, flags: int = EVAL_FULL):
         reqs = np.ascontiguousarray(reqs, dtype=POD_REQ)

@@ -1048,6 +1048,52 @@ extern "C" int yoda_normalize_scores(yoda_ctx *c, int64_t *scores, u32 n) {
 }
 
 // ------------------------------------------------------------------------------------------
+// QueueSort (sort.go:8-18): stable order of a pending batch by priority, higher first
+// ------------------------------------------------------------------------------------------
+__global__ void k_queue_keys(const i64 *__restrict__ pri, u32 n, u64 *keys, u32 *vals) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    // descending priority as ascending unsigned key: flip the sign bit (signed -> unsigned order), then complement
+    keys[i] = ~((u64)pri[i] ^ 0x8000000000000000ull);
+    vals[i] = i;
+}
+
+extern "C" int yoda_queue_order(yoda_ctx *c, const int64_t *priority, u32 n, u32 *order) {
+    if (!c || (n && (!priority || !order))) return fail(YODA_E_ARG, "null argument");
+    if (n == 0) return YODA_OK;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    cudaStream_t st = c->stream;
+    u64 *keys_in = nullptr, *keys_out = nullptr;
+    u32 *vals_in = nullptr, *vals_out = nullptr;
+    i64 *d_pri = nullptr;
+    void *tmp = nullptr;
+    size_t bytes = 0;
+    int rc = dev_alloc(&keys_in, n);
+    if (!rc) rc = dev_alloc(&keys_out, n);
+    if (!rc) rc = dev_alloc(&vals_in, n);
+    if (!rc) rc = dev_alloc(&vals_out, n);
+    if (!rc) rc = dev_alloc(&d_pri, n);
+    auto done = [&](int code) {
+        cudaStreamSynchronize(st);
+        dev_free(keys_in); dev_free(keys_out); dev_free(vals_in); dev_free(vals_out); dev_free(d_pri);
+        if (tmp) cudaFree(tmp);
+        return code;
+    };
+    if (rc) return done(rc);
+    if (cub::DeviceRadixSort::SortPairs(nullptr, bytes, keys_in, keys_out, vals_in, vals_out, (int)n, 0, 64, st) != cudaSuccess ||
+        cudaMalloc(&tmp, std::max<size_t>(bytes, 16)) != cudaSuccess)
+        return done(fail(YODA_E_NOMEM, "sort scratch allocation failed"));
+    if (cudaMemcpyAsync(d_pri, priority, (size_t)n * 8, cudaMemcpyHostToDevice, st) != cudaSuccess) return done(fail(YODA_E_CUDA, "H2D failed"));
+    k_queue_keys<<<(n + 255) / 256, 256, 0, st>>>(d_pri, n, keys_in, vals_in);
+    if (cub::DeviceRadixSort::SortPairs(tmp, bytes, keys_in, keys_out, vals_in, vals_out, (int)n, 0, 64, st) != cudaSuccess)  // LSD radix: stable
+        return done(fail(YODA_E_CUDA, "radix sort failed"));
+    if (cudaMemcpyAsync(order, vals_out, (size_t)n * 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) return done(fail(YODA_E_CUDA, "D2H failed"));
+    if (cudaStreamSynchronize(st) != cudaSuccess) return done(fail(YODA_E_CUDA, "queue order failed: %s", cudaGetErrorString(cudaGetLastError())));
+    return done(YODA_OK);
+}
+
+// ------------------------------------------------------------------------------------------
 // label parsing (host): strconv.Atoi with error -> 0, then the uint/uint64 conversion
 // ------------------------------------------------------------------------------------------
 extern "C" uint64_t yoda_parse_label(const char *s, size_t len) {
