@@ -150,6 +150,15 @@ int yoda_result_matrices(yoda_ctx *ctx, void **d_bits, void **d_raw, void **d_no
  * used when the framework's list is not Yoda's own feasible set (other plugins filtered too). */
 int yoda_normalize_scores(yoda_ctx *ctx, int64_t *scores, uint32_t n);
 
+/* Sequential-commit batch: what a run of single-pod cycles does.  Pods are taken in `order` (NULL =
+ * 0..n-1, e.g. the output of yoda_queue_order); after each choice the chosen node's allocateMemorySum
+ * grows by the pod's StrToUint64(scv/memory) -- kube-scheduler's assume step, which the next cycle's
+ * CalculateAllocateScore sees through NodeInfo.Pods (algorithm.go:74-87) -- before the next pod is
+ * evaluated.  out[p] (indexed like `pods`) is the pod's cycle on the state it met: maxima, lowest,
+ * highest, feasible count, chosen node.  The committed snapshot is not modified: the caller records
+ * real bindings with yoda_node_set_alloc.  Needs a narrow snapshot and an unsharded context. */
+int yoda_eval_sequential(yoda_ctx *ctx, const yoda_pod_req *pods, uint32_t n_pods, const uint32_t *order, yoda_pod_result *out);
+
 /* QueueSort for a pending batch: sort.Less / sort.GetPodPriority (pkg/yoda/sort/sort.go:8-18, wired at
  * scheduler.go:105-107) order pods by the scv/priority label, higher first.  Given the priorities
  * (host parses the label: strconv.Atoi, value kept even on a range error, 0 without the label), writes

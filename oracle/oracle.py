@@ -44,6 +44,7 @@ def lib():
         L.ora_filter.argtypes = [C.c_void_p, C.c_uint32, C.c_char_p, C.c_char_p, C.c_char_p]
         L.ora_node_static.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
         L.ora_score_with_max.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ora_eval_sequential.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 9
         L.ora_pod_priority.restype = C.c_int64
         L.ora_pod_priority.argtypes = [C.c_char_p]
         L.ora_queue_order.argtypes = [C.c_uint32, C.c_void_p, C.c_void_p]
@@ -158,6 +159,20 @@ class OracleCluster:
         rc = lib().ora_score_with_max(self._h, enc("scv/number"), enc("scv/memory"), enc("scv/clock"), mx.ctypes.data, feas.ctypes.data, raw.ctypes.data)
         assert rc == 0, rc
         return feas, raw
+
+    def eval_sequential(self, pods: Sequence[dict], order=None) -> dict:
+        """Single-pod cycles in `order`, each pod assumed onto its chosen node before the next one."""
+        P = len(pods)
+        num = _cstr_array([d.get("scv/number") for d in pods])
+        mem = _cstr_array([d.get("scv/memory") for d in pods])
+        clk = _cstr_array([d.get("scv/clock") for d in pods])
+        o = None if order is None else np.ascontiguousarray(order, dtype=np.uint32)
+        out = {"max6": np.zeros((P, 6), np.uint64), "lowest": np.zeros(P, np.int64), "highest": np.zeros(P, np.int64),
+               "count": np.zeros(P, np.uint32), "chosen": np.zeros(P, np.int32)}
+        rc = lib().ora_eval_sequential(self._h, P, C.cast(num, C.c_void_p), C.cast(mem, C.c_void_p), C.cast(clk, C.c_void_p), _p(o),
+                                       _p(out["max6"]), _p(out["lowest"]), _p(out["highest"]), _p(out["count"]), _p(out["chosen"]))
+        assert rc == 0, rc
+        return out
 
     def eval(self, pods: Sequence[dict], faithful: bool = False, threads: int = 1, full: bool = True) -> dict:
         """pods: list of label dicts (keys scv/number, scv/memory, scv/clock; others ignored)."""

@@ -687,3 +687,52 @@ void ora_queue_order(uint32_t n, const char *const *priority_labels, uint32_t *o
     }
     free(pri);
 }
+
+/* Sequential-commit batch: a run of single-pod scheduling cycles.  Pods are taken in `order` (NULL =
+ * as given); after each cycle the pod is "assumed" onto its chosen node, i.e. appended to that node's
+ * NodeInfo.Pods, which is what CalculateAllocateScore (algorithm.go:74-87) reads in the next cycle.
+ * The cluster is restored before returning.  Outputs indexed by pod (not by order). */
+int ora_eval_sequential(ora_cluster *cl, uint32_t n_pods, const char *const *number, const char *const *memory,
+                        const char *const *clock, const uint32_t *order, uint64_t *max6, int64_t *lowest, int64_t *highest,
+                        uint32_t *count, int32_t *chosen) {
+    const uint32_t N = cl->n_nodes;
+    uint32_t *orig_np = (uint32_t *)malloc(sizeof(uint32_t) * (N ? N : 1));
+    for (uint32_t n = 0; n < N; ++n) orig_np[n] = cl->nodes[n].n_pods;
+    ora_labels *pods = (ora_labels *)calloc(n_pods ? n_pods : 1, sizeof(ora_labels));
+    for (uint32_t p = 0; p < n_pods; ++p) {
+        const char *keys[3], *vals[3];
+        uint32_t k = 0;
+        if (memory && memory[p]) { keys[k] = "scv/memory"; vals[k++] = memory[p]; }
+        if (number && number[p]) { keys[k] = "scv/number"; vals[k++] = number[p]; }
+        if (clock && clock[p]) { keys[k] = "scv/clock"; vals[k++] = clock[p]; }
+        labels_set(&pods[p], k, keys, vals);
+    }
+    ora_job j;
+    memset(&j, 0, sizeof j);
+    j.cl = cl; j.n_pods = n_pods; j.pods = pods;
+    j.max6 = max6; j.lowest = lowest; j.highest = highest; j.count = count; j.chosen = chosen;
+    uint8_t *feas = (uint8_t *)malloc(N ? N : 1);
+    int64_t *raw = (int64_t *)malloc(sizeof(int64_t) * (N ? N : 1));
+    int64_t *list = (int64_t *)malloc(sizeof(int64_t) * (N ? N : 1));
+    int rc = ORA_OK;
+    for (uint32_t k = 0; k < n_pods && !rc; ++k) {
+        const uint32_t p = order ? order[k] : k;
+        rc = eval_one_pod(&j, p, feas, raw, list);
+        if (!rc && chosen[p] >= 0) { /* assume: the pod now runs on the chosen node */
+            ora_node *nd = &cl->nodes[chosen[p]];
+            nd->pods = (ora_labels *)realloc(nd->pods, sizeof(ora_labels) * (nd->n_pods + 1));
+            memset(&nd->pods[nd->n_pods], 0, sizeof(ora_labels));
+            const char *keys[3], *vals[3];
+            for (uint32_t q = 0; q < pods[p].n; ++q) { keys[q] = pods[p].kv[q].key; vals[q] = pods[p].kv[q].val; }
+            labels_set(&nd->pods[nd->n_pods], pods[p].n, keys, vals);
+            nd->n_pods++;
+        }
+    }
+    for (uint32_t n = 0; n < N; ++n) { /* restore */
+        ora_node *nd = &cl->nodes[n];
+        while (nd->n_pods > orig_np[n]) labels_free(&nd->pods[--nd->n_pods]);
+    }
+    for (uint32_t p = 0; p < n_pods; ++p) labels_free(&pods[p]);
+    free(pods); free(feas); free(raw); free(list); free(orig_np);
+    return rc;
+}

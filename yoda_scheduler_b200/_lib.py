@@ -51,6 +51,7 @@ SYMBOLS = {
     "yoda_last_timing": (_I, [_P, C.POINTER(Timing)]),
     "yoda_result_matrices": (_I, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_U64)]),
     "yoda_normalize_scores": (_I, [_P, _P, _U32]),
+    "yoda_eval_sequential": (_I, [_P, _P, _U32, _P, _P]),
     "yoda_queue_order": (_I, [_P, _P, _U32, _P]),
     "yoda_normalize_scores_noalloc": (_I, [_P, _P, _U32, _P]),
     "yoda_parse_label": (_U64, [C.c_char_p, C.c_size_t]),

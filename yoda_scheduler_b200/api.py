@@ -127,6 +127,14 @@ class Context:
         check(self.L.yoda_normalize_scores(self.h, a.ctypes.data, len(a)))
         return a
 
+    def eval_sequential(self, reqs: np.ndarray, order=None) -> np.ndarray:
+        """One pod after the other, each choice committed to the chosen node's allocateMemorySum first."""
+        reqs = np.ascontiguousarray(reqs, dtype=POD_REQ)
+        out = np.zeros(len(reqs), POD_RES)
+        o = None if order is None else np.ascontiguousarray(order, dtype=np.uint32)
+        check(self.L.yoda_eval_sequential(self.h, reqs.ctypes.data, len(reqs), None if o is None else o.ctypes.data, out.ctypes.data))
+        return out
+
     def queue_order(self, priorities) -> np.ndarray:
         """Batch consumption order under sort.Less (scv/priority, higher first, stable)."""
         pri = np.ascontiguousarray(priorities, dtype=np.int64)

@@ -17,6 +17,7 @@
 #include "common.cuh"
 #include "direct_kernels.cuh"
 #include "fast_kernels.cuh"
+#include "seq_kernels.cuh"
 
 // ------------------------------------------------------------------------------------------
 // errors
@@ -145,7 +146,12 @@ struct yoda_ctx {
     FastCtl *fw_ctl = nullptr, *fw_hctl = nullptr;
     u32 fw_n_groups = 0, fw_n_classes = 0;
     bool fw_small = false, fw_allow_defer = false, fw_deferred_err = false;
-    bool fw_decide_merged = false;  // DECIDE on one GPU: the score pass also yields counts and the node choice
+    bool fw_decide_merged = false;
+    // sequential-commit scratch
+    u64 *sq_alloc = nullptr;
+    u32 *sq_stat = nullptr, *sq_pos = nullptr, *sq_order = nullptr, *sq_status = nullptr;
+    u32 sq_pods_cap = 0;
+    int n_sms = 0;  // DECIDE on one GPU: the score pass also yields counts and the node choice
 };
 
 #define FAST_CLASS_CAP 4096u
@@ -212,6 +218,7 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
     if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess)
         return bail(fail(YODA_E_CUDA, "cudaStreamCreate failed"));
     c->stream = c->own_stream;
+    if (cudaDeviceGetAttribute(&c->n_sms, cudaDevAttrMultiProcessorCount, cfg->device) != cudaSuccess || c->n_sms <= 0) c->n_sms = 148;
     for (int i = 0; i < EV_COUNT; ++i)
         if (cudaEventCreate(&c->ev[i]) != cudaSuccess) return bail(fail(YODA_E_CUDA, "cudaEventCreate failed"));
     const u32 cap = round_up(cfg->max_nodes, 128);
@@ -270,6 +277,7 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     dev_free(c->fw_slot); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
     dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_gdesc); dev_free(c->fw_pods);
     dev_free(c->fw_m_sorted); dev_free(c->fw_step); dev_free(c->fw_cls_max); dev_free(c->fw_tables); dev_free(c->fw_ctl);
+    dev_free(c->sq_alloc); dev_free(c->sq_stat); dev_free(c->sq_pos); dev_free(c->sq_order); dev_free(c->sq_status);
     if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
     if (c->fw_hctl) cudaFreeHost(c->fw_hctl);
     if (c->h_upd) cudaFreeHost(c->h_upd);
@@ -892,6 +900,80 @@ extern "C" int yoda_eval_batch_device(yoda_ctx *c, const void *d_pods, u32 P, u3
     }
     if (d_out)
         CU(cudaMemcpyAsync(d_out, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToDevice, c->stream));
+    return YODA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// sequential-commit batch (seq_kernels.cuh)
+// ------------------------------------------------------------------------------------------
+extern "C" int yoda_eval_sequential(yoda_ctx *c, const yoda_pod_req *pods, u32 P, const u32 *order, yoda_pod_result *out) {
+    if (!c || (P && (!pods || !out))) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (P == 0) return YODA_OK;
+    if (c->comm) return fail(YODA_E_STATE, "sequential-commit evaluation is not available on a node-sharded context");
+    TRY(begin_locked(c, P, YODA_EVAL_DECIDE));
+    if (c->ph_path != 1)
+        return fail(YODA_E_RANGE, "sequential-commit evaluation needs a narrow snapshot (card fields < 2^32-1, static scores < 2^24)");
+    cudaStream_t st = c->stream;
+    if (!c->sq_alloc) {
+        TRY(dev_alloc(&c->sq_alloc, c->snap.cap));
+        TRY(dev_alloc(&c->sq_stat, c->snap.cap));
+        TRY(dev_alloc(&c->sq_status, 1));
+    }
+    if (P > c->sq_pods_cap) {
+        CU(cudaStreamSynchronize(st));
+        dev_free(c->sq_pos);
+        dev_free(c->sq_order);
+        c->sq_pods_cap = 0;
+        TRY(dev_alloc(&c->sq_pos, c->pods_cap));
+        TRY(dev_alloc(&c->sq_order, c->pods_cap));
+        c->sq_pods_cap = c->pods_cap;
+    }
+    CU(cudaMemcpyAsync(c->d_req, pods, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, st));
+    if (order) {
+        for (u32 i = 0; i < P; ++i)
+            if (order[i] >= P) return fail(YODA_E_ARG, "order[%u] = %u is not a pod of this batch", i, order[i]);
+        CU(cudaMemcpyAsync(c->sq_order, order, (size_t)P * sizeof(u32), cudaMemcpyHostToDevice, st));
+    }
+    c->fw_allow_defer = false;
+    c->fw_deferred_err = false;
+    c->fw_decide_merged = true;  // the choice comes out as a packed (score, index) key, as in merged DECIDE
+    // maxima, groups, classes and class tables do not depend on allocations: same kernels as the frozen path
+    TRY(phase0(c, c->d_req));
+    if (c->ph_path == 1) TRY(fast_classes(c));
+    if (c->ph_path != 1)
+        return fail(YODA_E_RANGE, "sequential-commit evaluation needs the table path (too many requirement groups or classes in this batch)");
+    CU(cudaEventRecord(c->ev[EV_SCORE], st));
+    const u32 N = c->snap.n_nodes;
+    if (N) {
+        k_seq_positions<<<(P + 255) / 256, 256, 0, st>>>(c->fw_pods, P, c->sq_pos);
+        LAUNCHED(c);
+        k_seq_init<<<(N + 255) / 256, 256, 0, st>>>(c->snap, c->sq_alloc, c->sq_stat);
+        LAUNCHED(c);
+        CU(cudaMemsetAsync(c->sq_status, 0, sizeof(u32), st));
+        int per_sm = 0;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_seq_commit, SEQ_THREADS, 0));
+        const u32 grid = std::max(1u, std::min<u32>((N + SEQ_THREADS - 1) / SEQ_THREADS, (u32)per_sm * (u32)c->n_sms));
+        DevSnap snap = c->snap;
+        const PodS *a_pods = c->fw_pods;
+        const PodC *a_podc = c->d_pods;
+        const u32 *a_pos = c->sq_pos, *a_order = order ? c->sq_order : nullptr, *a_tables = c->fw_tables;
+        u32 a_P = P;
+        void *args[] = {&snap, &a_pods, &a_podc, &a_pos, &a_order, &a_P, &a_tables, &c->sq_alloc, &c->sq_stat, &c->d_hilo, &c->d_count,
+                        &c->d_ckey, &c->sq_status};
+        CU(cudaLaunchCooperativeKernel((void *)k_seq_commit, dim3(grid), dim3(SEQ_THREADS), args, 0, st));
+        LAUNCHED(c);
+    }
+    TRY(phase3(c));
+    u32 status = 0;
+    CU(cudaMemcpyAsync(out, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
+    if (N) CU(cudaMemcpyAsync(&status, c->sq_status, sizeof(u32), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    c->fw_decide_merged = false;
+    c->ph_done = 3;
+    collect_timing(c, false);
+    if (status) return fail(YODA_E_RANGE, "a committed allocation pushed a node's static score out of the narrow range");
     return YODA_OK;
 }
 
