@@ -636,14 +636,16 @@ static dim3 hot_grid(const yoda_ctx *c, u32 n_pods) {
     return dim3((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (n_pods + HOT_CHUNK - 1) / HOT_CHUNK);
 }
 
+#define SCORE_NPL 4  // nodes per lane in the score pass (its per-node state is 7 registers)
 static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
+    const dim3 grid((c->snap.n_nodes + HOT_WARPS * SCORE_NPL * 32 - 1) / (HOT_WARPS * SCORE_NPL * 32), (p_end - p_begin + HOT_CHUNK - 1) / HOT_CHUNK);
     if (c->fw_decide_merged)
-        k_fast_score<4, true><<<hot_grid(c, p_end - p_begin), HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables,
-                                                                                         c->d_hilo, c->d_count, c->d_ckey);
+        k_fast_score<SCORE_NPL, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
+                                                                           c->d_count, c->d_ckey);
     else
-        k_fast_score<4, false><<<hot_grid(c, p_end - p_begin), HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables,
-                                                                                          c->d_hilo, c->d_count, c->d_ckey);
+        k_fast_score<SCORE_NPL, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
+                                                                            c->d_count, c->d_ckey);
     LAUNCHED(c);
     return YODA_OK;
 }
