@@ -444,7 +444,7 @@ template <int NPL>
 __device__ __forceinline__ void hot_load_nodes(NodeRegs<NPL> &r, const DevSnap &s, u32 base, u32 lane) {
 #pragma unroll
     for (int j = 0; j < NPL; ++j) {
-        const u32 n = base + j * 32 + lane;
+        const u32 n = base + (j >> 1) * 64 + 2 * lane + (j & 1);  // a lane owns pairs of adjacent nodes: 16-byte row pieces
         const bool in = n < s.n_nodes;
         const u32 nn = in ? n : 0;
         load8(s.n32[F_FREE] + (size_t)nn * G, r.fr[j]);
@@ -465,7 +465,7 @@ __device__ __forceinline__ void hot_load_class(NodeRegs<NPL> &r, const DevSnap &
                                                u32 reqC, u32 base, u32 lane) {
 #pragma unroll
     for (int j = 0; j < NPL; ++j) {
-        const u32 n = base + j * 32 + lane;
+        const u32 n = base + (j >> 1) * 64 + 2 * lane + (j & 1);
         const u32 nn = n < s.n_nodes ? n : 0;
         load8(tables + ((size_t)cls * s.cap + nn) * G, r.cs[j]);
         r.clkok[j] = true;
@@ -747,13 +747,15 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
     half_sync(bar_id);
     u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFEu, cur_m = 0, cur_lo = 0, cur_hi = 0;
     u64 raw64[NPL];                     // Score as stored (int64, high word 0)
-    u32 bound[NPL], fitm[NPL];          // validity bound per lane; feasible lanes of the slot (warp-uniform)
+    static_assert(NPL == 4, "the row layout below packs two pairs of adjacent nodes per lane");
+    u32 bound[NPL], fitm[NPL];          // validity bound per lane; feasible lanes of slot j (warp-uniform ballots)
+    u32 fitw[NPL] = {0, 0, 0, 0};       // the same bits in row order: word w = nodes base+32w .. base+32w+31
     u32 fitl[NPL], qn[NPL], rmax[NPL];  // lane mask (0 / ~0), normalized score, best feasible score of the slot
 #pragma unroll
     for (int j = 0; j < NPL; ++j) { raw64[j] = 0; bound[j] = 0; fitm[j] = 0; fitl[j] = 0; qn[j] = 0; rmax[j] = 0; }
     u32 cnt = 0, bmin = 0, wmax = 0;  // bmin: min bound over the lane's slots; wmax: best feasible score of the warp's nodes
-    unsigned long long *rawp = reinterpret_cast<unsigned long long *>(raw_out) + base + lane;
-    u8 *normp = norm_out + base + lane;
+    unsigned long long *rawp = reinterpret_cast<unsigned long long *>(raw_out) + base + 2 * lane;
+    u8 *normp = norm_out + base + 2 * lane;
     u32 *bitsp = bits_out + (base >> 5);
     for (u32 i = 0; i < cn; ++i) {
         const PodRegs pod = pod_from_smem(sm.sp, i);
@@ -787,6 +789,21 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
             bmin = bound[0];
 #pragma unroll
             for (int j = 1; j < NPL; ++j) bmin = min(bmin, bound[j]);
+            // node base + 64*(j>>1) + 2*lane + (j&1) is bit `lane` of ballot j: interleave pairs of ballots into row order
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                u32 word = 0;
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    u32 x = (fitm[2 * (w >> 1) + e] >> (16 * (w & 1))) & 0xFFFFu;  // lanes 16(w&1) .. +15
+                    x = (x | (x << 8)) & 0x00FF00FFu;                               // spread bit i to position 2i
+                    x = (x | (x << 4)) & 0x0F0F0F0Fu;
+                    x = (x | (x << 2)) & 0x33333333u;
+                    x = (x | (x << 1)) & 0x55555555u;
+                    word |= x << e;
+                }
+                fitw[w] = word;
+            }
         }
         if (WRITE && !nsame) {
             // scheduler.go:152: (raw - lo) * 100 / (hi - lo), exact via the 57-bit reciprocal
@@ -799,27 +816,21 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
         cur_m = pod.m; cur_lo = pn.x; cur_hi = pn.y;
         u32 best = 0xFFFFFFFFu;
         if (cnt && wmax == pn.y) {  // warp-uniform: some lane of this warp holds the pod's top score
+            u32 mine = 0xFFFFFFFFu;
 #pragma unroll
-            for (int j = NPL - 1; j >= 0; --j) {
-                const u32 topmask = __ballot_sync(0xFFFFFFFFu, fitl[j] && (u32)raw64[j] == pn.y);
-                if (topmask) best = base + j * 32 + (__ffs(topmask) - 1);
-            }
+            for (int j = NPL - 1; j >= 0; --j)
+                if (fitl[j] && (u32)raw64[j] == pn.y) mine = base + (j >> 1) * 64 + 2 * lane + (j & 1);
+            best = __reduce_min_sync(0xFFFFFFFFu, mine);
         }
         if (WRITE) {
             const size_t row = (size_t)pod.orig * stride;
-#pragma unroll
-            for (int j = 0; j < NPL; ++j) {
-                __stcs(rawp + row + j * 32, raw64[j]);   // streaming: written once, never re-read by this pass
-                __stcs(normp + row + j * 32, (u8)qn[j]);
-            }
-            if (lane == 0) {
-                u32 *bp = bitsp + (size_t)pod.orig * (stride >> 5);
-                if (NPL == 4) __stcs(reinterpret_cast<uint4 *>(bp), make_uint4(fitm[0], fitm[1], fitm[2], fitm[3]));
-                else if (NPL == 2) *reinterpret_cast<uint2 *>(bp) = make_uint2(fitm[0], fitm[1]);
-                else
-#pragma unroll
-                    for (int j = 0; j < NPL; ++j) bp[j] = fitm[j];
-            }
+            // streaming stores (written once, never re-read by this pass); every instruction covers whole sectors:
+            // 2 x 512 B of scores and 2 x 64 B of normalized scores per warp
+            __stcs(reinterpret_cast<ulonglong2 *>(rawp + row), make_ulonglong2(raw64[0], raw64[1]));
+            __stcs(reinterpret_cast<ulonglong2 *>(rawp + row + 64), make_ulonglong2(raw64[2], raw64[3]));
+            __stcs(reinterpret_cast<unsigned short *>(normp + row), (unsigned short)(qn[0] | (qn[1] << 8)));
+            __stcs(reinterpret_cast<unsigned short *>(normp + row + 64), (unsigned short)(qn[2] | (qn[3] << 8)));
+            if (lane == 0) __stcs(reinterpret_cast<uint4 *>(bitsp + (size_t)pod.orig * (stride >> 5)), make_uint4(fitw[0], fitw[1], fitw[2], fitw[3]));
         }
         if (lane == 0) {
             sm.cnt_s[warp][i] = cnt;
