@@ -117,6 +117,36 @@ func (c *Ctx) NormalizeScores(scores []int64) error {
 }
 
 
+// QueueOrder: batch order under sort.Less (scv/priority, higher first, stable).
+func (c *Ctx) QueueOrder(priority []int64) ([]uint32, error) {
+	order := make([]uint32, len(priority))
+	if len(priority) == 0 {
+		return order, nil
+	}
+	rc := C.yoda_queue_order(c.h, (*C.int64_t)(unsafe.Pointer(&priority[0])), C.uint32_t(len(priority)), (*C.uint32_t)(unsafe.Pointer(&order[0])))
+	if rc != 0 {
+		return nil, lastErr(rc)
+	}
+	return order, nil
+}
+
+// EvalSequential: pods in `order`, each choice added to the chosen node's allocateMemorySum before the next pod.
+func (c *Ctx) EvalSequential(pods []PodReq, order []uint32) ([]PodResult, error) {
+	out := make([]PodResult, len(pods))
+	if len(pods) == 0 {
+		return out, nil
+	}
+	var op *C.uint32_t
+	if order != nil {
+		op = (*C.uint32_t)(unsafe.Pointer(&order[0]))
+	}
+	rc := C.yoda_eval_sequential(c.h, (*C.yoda_pod_req)(unsafe.Pointer(&pods[0])), C.uint32_t(len(pods)), op, (*C.yoda_pod_result)(unsafe.Pointer(&out[0])))
+	if rc != 0 {
+		return nil, lastErr(rc)
+	}
+	return out, nil
+}
+
 // MakeRecord / MakeReq / Chosen: helpers for callers outside this package (cgo field names are
 // not exported across packages).
 func MakeRecord(cardNumber uint64, healthy uint32, free, total []uint64, clock, core, bandwidth, power uint64) *NodeRecord {

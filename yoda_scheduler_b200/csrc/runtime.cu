@@ -120,7 +120,6 @@ struct yoda_ctx {
     // phase state
     u32 ph_P = 0, ph_flags = 0;
     int ph_done = -1;
-    const yoda_pod_req *ph_dev_req = nullptr;
     // timing
     cudaEvent_t ev[EV_COUNT]{};
     yoda_timing timing{};

@@ -287,6 +287,25 @@ Status Yoda::EvalBatch(const std::vector<v1::Pod> &pods, bool full, std::vector<
         return NewStatus(framework::Error, yoda_last_error());
     return NewStatus(framework::Success);
 }
+Status Yoda::EvalSequential(const std::vector<v1::Pod> &pods, std::vector<yoda_pod_result> *out, std::vector<uint32_t> *order_out) {
+    Status s = Sync();
+    if (!s.IsSuccess()) return s;
+    std::vector<yoda_pod_req> reqs(pods.size());
+    std::vector<int64_t> pri(pods.size());
+    for (size_t i = 0; i < pods.size(); ++i) {
+        reqs[i] = Requirement(pods[i]);
+        pri[i] = GetPodPriority(framework::QueuedPodInfo{pods[i]});
+    }
+    std::vector<uint32_t> order(pods.size());
+    out->assign(pods.size(), yoda_pod_result{});
+    if (pods.empty()) return NewStatus(framework::Success);
+    std::lock_guard<std::mutex> lk(mu_);
+    if (yoda_queue_order(ctx_, pri.data(), (uint32_t)pri.size(), order.data()) != YODA_OK ||
+        yoda_eval_sequential(ctx_, reqs.data(), (uint32_t)reqs.size(), order.data(), out->data()) != YODA_OK)
+        return NewStatus(framework::Error, yoda_last_error());
+    if (order_out) *order_out = order;
+    return NewStatus(framework::Success);
+}
 int Yoda::FetchRow(uint32_t pod, int kind, void *dst, size_t bytes) {
     std::lock_guard<std::mutex> lk(mu_);
     return yoda_fetch_row(ctx_, pod, kind, dst, bytes);

@@ -54,6 +54,8 @@ class Yoda {
 
     // ---- batch evaluation used by the benchmark harness: one device pass for all pending pods ----
     framework::Status EvalBatch(const std::vector<v1::Pod> &pods, bool full, std::vector<yoda_pod_result> *out);
+    // one pod after the other in sort.Less order, every choice assumed onto its node before the next pod is scored
+    framework::Status EvalSequential(const std::vector<v1::Pod> &pods, std::vector<yoda_pod_result> *out, std::vector<uint32_t> *order = nullptr);
     int FetchRow(uint32_t pod, int kind, void *dst, size_t bytes);
     static yoda_pod_req Requirement(const v1::Pod &pod);  // label parsing, filter.go:11-50
     int32_t NodeIndex(const std::string &name) const;     // -1 if never seen
