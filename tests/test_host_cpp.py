@@ -54,11 +54,12 @@ def test_harness_framework_path_equals_batch_and_oracle(tmp_path):
     N, P, seed = 2000, 256, synth.SEED + 2
     exe = _build.build_host()
     dump = tmp_path / "batch.txt"
-    r = subprocess.run([exe, "--nodes", str(N), "--pods", str(P), "--pod-seed", str(seed), "--cycles", "24", "--dump", str(dump)],
+    r = subprocess.run([exe, "--nodes", str(N), "--pods", str(P), "--pod-seed", str(seed), "--cycles", "24", "--seq", "40", "--dump", str(dump)],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     info = json.loads(r.stdout.strip().splitlines()[-1])
     assert info["mismatches"] == 0 and info["cycles_checked"] == 24 and info["path"] == 1
+    assert info["seq_pods"] == 40 and info["seq_mismatches"] == 0   # sequential-commit pass == 40 real cycles with assume
     got = np.loadtxt(dump, dtype=np.int64).reshape(P, 5)
     want = ora.OracleCluster.from_snapshot(synth.make_snapshot(N)).eval(synth.make_pod_labels(P, seed), threads=8, full=False)
     assert np.array_equal(got[:, 0], want["chosen"])

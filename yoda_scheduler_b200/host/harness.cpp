@@ -36,7 +36,7 @@ static uint64_t fnv(uint64_t h, uint64_t v) {
 }
 
 int main(int argc, char **argv) {
-    uint64_t N = 2000, P = 256, pod_seed = synth::SEED + 2, cycles = 16;
+    uint64_t N = 2000, P = 256, pod_seed = synth::SEED + 2, cycles = 16, seq = 0;
     bool checksum = false;
     const char *dump = nullptr;
     for (int i = 1; i < argc; ++i) {
@@ -45,6 +45,7 @@ int main(int argc, char **argv) {
         else if (!strcmp(argv[i], "--pods")) P = next();
         else if (!strcmp(argv[i], "--pod-seed")) pod_seed = next();
         else if (!strcmp(argv[i], "--cycles")) cycles = next();
+        else if (!strcmp(argv[i], "--seq")) seq = next();
         else if (!strcmp(argv[i], "--checksum")) checksum = true;
         else if (!strcmp(argv[i], "--dump") && i + 1 < argc) dump = argv[++i];
     }
@@ -144,13 +145,52 @@ int main(int argc, char **argv) {
     }
     const double cycle_ms = cycles ? ms_since(t0) / (double)cycles : 0.0;
 
+    // ---- (3) sequential commit: one device pass for the first `seq` pods against the real thing -- one
+    //         framework cycle per pod with the pod assumed onto its node (OnPodAdd) before the next cycle
+    int seq_mismatches = 0;
+    double seq_ms = 0.0;
+    seq = std::min<uint64_t>(seq, P);
+    if (seq) {
+        std::vector<v1::Pod> head(pods.begin(), pods.begin() + seq);
+        std::vector<yoda_pod_result> sres;
+        t0 = Clock::now();
+        auto sst = plugin->EvalSequential(head, &sres);
+        seq_ms = ms_since(t0);
+        if (!sst.IsSuccess()) { fprintf(stderr, "EvalSequential: %s\n", sst.message.c_str()); return 2; }
+        std::vector<std::pair<std::string, uint64_t>> assumed;
+        for (uint64_t p = 0; p < seq; ++p) {
+            framework::CycleState state;
+            std::vector<std::string> feasible;
+            for (const auto &nd : nodes)
+                if (plugin->Filter(state, head[p], *handle.GetNodeInfo(nd.scv.Name)).IsSuccess()) feasible.push_back(nd.scv.Name);
+            plugin->PostFilter(state, head[p]);
+            int32_t chosen = -1;
+            if (!feasible.empty()) {
+                framework::NodeScoreList scores;
+                for (const auto &nm : feasible) scores.push_back({nm, plugin->Score(state, head[p], nm).first});
+                plugin->NormalizeScore(state, head[p], scores);
+                int64_t best = -1;
+                for (const auto &sc : scores)
+                    if (sc.Score > best) { best = sc.Score; chosen = plugin->NodeIndex(sc.Name); }
+            }
+            if (chosen != sres[p].chosen) seq_mismatches++;
+            if (chosen >= 0) {  // assume: the pod now counts towards the node's allocateMemorySum
+                plugin->OnPodAdd(plugin->NodeName((uint32_t)chosen), head[p]);
+                assumed.push_back({plugin->NodeName((uint32_t)chosen), p});
+            }
+        }
+        for (const auto &a : assumed) plugin->OnPodDelete(a.first, head[a.second]);  // undo
+        plugin->Sync();
+        mismatches += seq_mismatches;
+    }
+
     if (dump) {
         std::ofstream f(dump);
         for (const auto &r : batch) f << r.chosen << " " << r.feasible << " " << r.lowest << " " << r.highest << " " << r.max_free_memory << "\n";
     }
     printf("{\"nodes\": %llu, \"pods\": %llu, \"load_ms\": %.3f, \"batch_ms\": %.3f, \"batch_device_ms\": %.3f, \"evals_per_s\": %.4g, "
-           "\"framework_cycle_ms\": %.3f, \"cycles_checked\": %llu, \"mismatches\": %d, \"path\": %u}\n",
+           "\"framework_cycle_ms\": %.3f, \"cycles_checked\": %llu, \"seq_pods\": %llu, \"seq_ms\": %.3f, \"seq_mismatches\": %d, \"mismatches\": %d, \"path\": %u}\n",
            (unsigned long long)N, (unsigned long long)P, load_ms, batch_ms, tm.total_ms, (double)N * (double)P / (batch_ms * 1e-3), cycle_ms,
-           (unsigned long long)cycles, mismatches, tm.path);
+           (unsigned long long)cycles, (unsigned long long)seq, seq_ms, seq_mismatches, mismatches, tm.path);
     return mismatches ? 1 : 0;
 }
