@@ -350,3 +350,32 @@ def test_class_table_overflow_falls_back(n_pods):
     res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_FULL)
     assert t.path == 0
     assert_matches_oracle(snap, labels, res, mats)
+
+
+def test_context_reuse_across_batch_sizes_and_modes():
+    """One long-lived context, batches of very different sizes and modes back to back (workspace growth,
+    small-batch path after the table path and vice versa, sequential mode in between): every answer must
+    equal the one a fresh context gives."""
+    N = 4000
+    snap = synth.make_snapshot(N)
+    all_reqs = synth.make_requests(30000, 77)
+    plan = [(5, api.EVAL_FULL), (3000, api.EVAL_FULL), (8, api.EVAL_DECIDE), (30000, api.EVAL_DECIDE), (1, api.EVAL_FULL),
+            (100, api.EVAL_FULL | api.EVAL_FORCE_DIRECT), (9, api.EVAL_FULL), (2500, api.EVAL_DECIDE), (2, api.EVAL_FULL)]
+    with api.Context(N) as ctx:
+        ctx.load_snapshot(snap)
+        for k, (p, flags) in enumerate(plan):
+            reqs = all_reqs[k * 7:k * 7 + p]
+            got = ctx.eval(reqs, flags)
+            rows = ctx.fetch_all(min(p, 3)) if flags & api.EVAL_FULL else None
+            if k == 3:
+                seq = ctx.eval_sequential(all_reqs[:500])
+            with api.Context(N) as fresh:
+                fresh.load_snapshot(snap)
+                want = fresh.eval(reqs, flags)
+                assert np.array_equal(got, want), (k, p, flags)
+                if rows is not None:
+                    w = fresh.fetch_all(min(p, 3))
+                    for key in rows:
+                        assert np.array_equal(rows[key], w[key]), (k, key)
+                if k == 3:
+                    assert np.array_equal(seq, fresh.eval_sequential(all_reqs[:500]))
