@@ -207,9 +207,15 @@ __global__ void k_build_sorted(const PodC *__restrict__ pods, u32 P, const u64 *
 // ------------------------------------------------------------------------------------------
 #define MAXT 128
 #define MAXG_TILE 8  // group descriptors staged per shared-memory tile
-__global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupDesc *__restrict__ gdesc, u32 n_groups,
-                                                         const u32 *__restrict__ m_sorted, u32 *step, u32 P) {
+// The group count is taken from the device (ctl) when the host has not read it back (one-GPU batches
+// run without that round trip); grids are then sized for the worst case and surplus blocks leave at once.
+__device__ __forceinline__ u32 group_count(const FastCtl *ctl, u32 n_groups) { return ctl ? min(ctl->n_groups, FAST_GROUP_CAP) : n_groups; }
+
+__global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupDesc *__restrict__ gdesc, u32 n_groups_host,
+                                                         const FastCtl *__restrict__ ctl, const u32 *__restrict__ m_sorted, u32 *step, u32 P) {
     __shared__ GroupDesc sg[MAXG_TILE];
+    const u32 n_groups = group_count(ctl, n_groups_host);
+    if (blockIdx.y * MAXG_TILE >= n_groups) return;
     const u32 n = blockIdx.x * MAXT + threadIdx.x;
     const bool live = n < s.n_nodes;
     const u32 nn = live ? n : 0;
@@ -289,40 +295,43 @@ __global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupD
 
 // one CTA per (group, field): suffix maximum over the group's pod segment, result max(1, .) into max6[orig]
 #define SCANT 1024
-__global__ void __launch_bounds__(SCANT) k_max_scan(const GroupDesc *__restrict__ gdesc, u32 n_groups, const u32 *__restrict__ step,
-                                                    const PodS *__restrict__ pods, u64 *max6, u32 P) {
-    const u32 gid = blockIdx.x, f = blockIdx.y;
-    if (gid >= n_groups) return;
-    const GroupDesc gd = gdesc[gid];
+__global__ void __launch_bounds__(SCANT) k_max_scan(const GroupDesc *__restrict__ gdesc, u32 n_groups_host, const FastCtl *__restrict__ ctl,
+                                                    const u32 *__restrict__ step, const PodS *__restrict__ pods, u64 *max6, u32 P) {
     __shared__ u32 warp_max[SCANT / 32];
     __shared__ u32 carry_s;
+    const u32 n_groups = group_count(ctl, n_groups_host);
+    const u32 f = blockIdx.y;
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) carry_s = 0;
-    __syncthreads();
     const u32 *sf = step + (size_t)f * P;
-    // walk the segment backwards in tiles of SCANT; thread t handles position top-1-t of the tile
-    for (u32 top = gd.seg_end; top > gd.seg_start;) {
-        const u32 cnt = min(SCANT, top - gd.seg_start);
-        const bool live = threadIdx.x < cnt;
-        const u32 pos = live ? top - 1 - threadIdx.x : 0;
-        u32 v = live ? sf[pos] : 0u;
-        // inclusive prefix max over threadIdx (= suffix max over positions)
+    for (u32 gid = blockIdx.x; gid < n_groups; gid += gridDim.x) {
+        const GroupDesc gd = gdesc[gid];
+        __syncthreads();
+        if (threadIdx.x == 0) carry_s = 0;
+        __syncthreads();
+        // walk the segment backwards in tiles of SCANT; thread t handles position top-1-t of the tile
+        for (u32 top = gd.seg_end; top > gd.seg_start;) {
+            const u32 cnt = min(SCANT, top - gd.seg_start);
+            const bool live = threadIdx.x < cnt;
+            const u32 pos = live ? top - 1 - threadIdx.x : 0;
+            u32 v = live ? sf[pos] : 0u;
+            // inclusive prefix max over threadIdx (= suffix max over positions)
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const u32 t = __shfl_up_sync(0xFFFFFFFFu, v, o);
-            if (lane >= (u32)o) v = max(v, t);
+            for (int o = 1; o < 32; o <<= 1) {
+                const u32 t = __shfl_up_sync(0xFFFFFFFFu, v, o);
+                if (lane >= (u32)o) v = max(v, t);
+            }
+            if (lane == 31) warp_max[warp] = v;
+            __syncthreads();
+            u32 pre = carry_s;
+            for (u32 w = lane; w < warp; w += 32) pre = max(pre, warp_max[w]);
+            pre = __reduce_max_sync(0xFFFFFFFFu, pre);
+            v = max(v, pre);
+            if (live) max6[(size_t)pods[pos].orig * 6 + f] = (u64)max(v, 1u);  // collection.go:31-38
+            __syncthreads();
+            if (threadIdx.x == SCANT - 1) carry_s = v;
+            __syncthreads();
+            top -= cnt;
         }
-        if (lane == 31) warp_max[warp] = v;
-        __syncthreads();
-        u32 pre = carry_s;
-        for (u32 w = lane; w < warp; w += 32) pre = max(pre, warp_max[w]);
-        pre = __reduce_max_sync(0xFFFFFFFFu, pre);
-        v = max(v, pre);
-        if (live) max6[(size_t)pods[pos].orig * 6 + f] = (u64)max(v, 1u);  // collection.go:31-38
-        __syncthreads();
-        if (threadIdx.x == SCANT - 1) carry_s = v;
-        __syncthreads();
-        top -= cnt;
     }
 }
 

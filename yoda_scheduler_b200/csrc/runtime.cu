@@ -146,6 +146,7 @@ struct yoda_ctx {
     u32 fw_n_groups = 0, fw_n_classes = 0;
     bool fw_small = false, fw_allow_defer = false, fw_deferred_err = false;
     bool fw_decide_merged = false;
+    bool fw_groups_pending = false;  // the group count (and its capacity check) has not been read back yet
     // sequential-commit scratch
     u64 *sq_alloc = nullptr;
     u32 *sq_stat = nullptr, *sq_pos = nullptr, *sq_order = nullptr, *sq_status = nullptr;
@@ -589,10 +590,10 @@ static int fast_phase0(yoda_ctx *c) {
         CU(cudaEventRecord(c->ev[EV_PREP], st));
         CU(cudaMemsetAsync(c->fw_step, 0, (size_t)P * 6 * sizeof(u32), st));
         if (N) {
-            k_max_thresholds<<<dim3((N + MAXT - 1) / MAXT, 1), MAXT, 0, st>>>(c->snap, c->fw_gdesc, P, c->fw_m_sorted, c->fw_step, P);
+            k_max_thresholds<<<dim3((N + MAXT - 1) / MAXT, 1), MAXT, 0, st>>>(c->snap, c->fw_gdesc, P, nullptr, c->fw_m_sorted, c->fw_step, P);
             LAUNCHED(c);
         }
-        k_max_scan<<<dim3(P, 6), SCANT, 0, st>>>(c->fw_gdesc, P, c->fw_step, c->fw_pods, c->d_max6, P);
+        k_max_scan<<<dim3(P, 6), SCANT, 0, st>>>(c->fw_gdesc, P, nullptr, c->fw_step, c->fw_pods, c->d_max6, P);
         LAUNCHED(c);
         return YODA_OK;
     }
@@ -602,12 +603,21 @@ static int fast_phase0(yoda_ctx *c) {
     LAUNCHED(c);
     k_hash_compact<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_gkeys, c->fw_gids, c->fw_htab, &c->fw_ctl->n_groups);
     LAUNCHED(c);
-    TRY(fast_read_ctl(c));
-    c->fw_n_groups = c->fw_hctl->n_groups;
-    if (c->fw_n_groups > FAST_GROUP_CAP) {
-        c->ph_path = 0;
-        return YODA_OK;
+    // On one GPU the group count stays on the device until the class count is read back (fast_classes):
+    // the kernels below take it from ctl.  Sharded / phase-split evaluations read it now, because the
+    // maxima are exchanged right after this phase and a fallback decided later could not undo that.
+    const bool count_on_device = c->fw_allow_defer;
+    u32 groups_bound = std::min(P, FAST_GROUP_CAP);
+    if (!count_on_device) {
+        TRY(fast_read_ctl(c));
+        c->fw_n_groups = c->fw_hctl->n_groups;
+        if (c->fw_n_groups > FAST_GROUP_CAP) {
+            c->ph_path = 0;
+            return YODA_OK;
+        }
+        groups_bound = c->fw_n_groups;
     }
+    const FastCtl *dctl = count_on_device ? c->fw_ctl : nullptr;
     k_group_assign<<<pb, 256, 0, st>>>(c->d_pods, P, c->fw_slot, c->fw_gids, c->fw_gdesc, FAST_GROUP_CAP, c->fw_keys_in, c->fw_vals_in,
                                        c->fw_ctl);
     LAUNCHED(c);
@@ -621,12 +631,14 @@ static int fast_phase0(yoda_ctx *c) {
     CU(cudaEventRecord(c->ev[EV_PREP], st));
     CU(cudaMemsetAsync(c->fw_step, 0, (size_t)P * 6 * sizeof(u32), st));
     if (N) {
-        const dim3 grid((N + MAXT - 1) / MAXT, std::max(1u, std::min(32u, (c->fw_n_groups + MAXG_TILE - 1) / MAXG_TILE)));
-        k_max_thresholds<<<grid, MAXT, 0, st>>>(c->snap, c->fw_gdesc, c->fw_n_groups, c->fw_m_sorted, c->fw_step, P);
+        const dim3 grid((N + MAXT - 1) / MAXT, std::max(1u, std::min(32u, (groups_bound + MAXG_TILE - 1) / MAXG_TILE)));
+        k_max_thresholds<<<grid, MAXT, 0, st>>>(c->snap, c->fw_gdesc, groups_bound, dctl, c->fw_m_sorted, c->fw_step, P);
         LAUNCHED(c);
     }
-    k_max_scan<<<dim3(c->fw_n_groups, 6), SCANT, 0, st>>>(c->fw_gdesc, c->fw_n_groups, c->fw_step, c->fw_pods, c->d_max6, P);
+    k_max_scan<<<dim3(std::max(1u, std::min(groups_bound, 2u * (u32)c->n_sms)), 6), SCANT, 0, st>>>(c->fw_gdesc, groups_bound, dctl, c->fw_step,
+                                                                                                   c->fw_pods, c->d_max6, P);
     LAUNCHED(c);
+    c->fw_groups_pending = count_on_device;
     return YODA_OK;
 }
 
@@ -702,6 +714,17 @@ static int fast_classes(yoda_ctx *c) {
     LAUNCHED(c);
     TRY(fast_read_ctl(c));
     c->fw_n_classes = c->fw_hctl->n_classes;
+    if (c->fw_groups_pending) {
+        c->fw_groups_pending = false;
+        c->fw_n_groups = c->fw_hctl->n_groups;
+        if (c->fw_n_groups > FAST_GROUP_CAP) {  // too many groups: the maxima of phase 0 are void, redo them exactly
+            c->ph_path = 0;
+            k_init_partials<<<(P + 255) / 256, 256, 0, st>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, P);
+            LAUNCHED(c);
+            TRY(direct_pods_launch(c, 0));
+            return YODA_OK;
+        }
+    }
     if (c->fw_hctl->err || c->fw_n_classes > ccap) {
         c->ph_path = 0;
         return YODA_OK;
@@ -717,6 +740,10 @@ static int fast_classes(yoda_ctx *c) {
         dim3 grid((N + CLST - 1) / CLST, c->fw_n_classes);
         k_class_tables<<<grid, CLST, 0, st>>>(c->snap, c->fw_cls_max, c->fw_n_classes, c->fw_tables, c->fw_ctl);
         LAUNCHED(c);
+    }
+    if (c->fw_allow_defer) {
+        c->fw_deferred_err = true;  // "every class fits the packed table": read back with the results
+        return YODA_OK;
     }
     TRY(fast_read_ctl(c));
     if (c->fw_hctl->err) {
@@ -783,6 +810,7 @@ static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
     if (c->ph_path == 1) TRY(ensure_fast(c, P));
     c->ph_P = P;
     c->ph_flags = flags;
+    c->fw_groups_pending = false;
     c->ph_done = -1;
     c->last_P = 0;
     c->last_full = false;
@@ -1041,6 +1069,7 @@ extern "C" int yoda_phase_begin(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u3
     c->fw_allow_defer = false;
     c->fw_deferred_err = false;
     c->fw_decide_merged = false;
+    c->fw_groups_pending = false;
     CU(cudaMemcpyAsync(c->d_req, pods, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));  // caller's buffer may be pageable and is not retained
     return YODA_OK;
