@@ -108,10 +108,10 @@ def workload(args, rank, world):
     return n_nodes, n_pods, pod_seed
 
 
-def cpu_arm(snap, labels_fn, n_nodes, threads, target_s, faithful=True):
+def cpu_arm(snap, labels_fn, n_nodes, threads, target_s, faithful=True, cl=None):
     """Time the oracle (CPU restatement of the Go plugin) on a bounded pod sample x all nodes."""
     from oracle import oracle as ora
-    cl = ora.OracleCluster.from_snapshot(snap)
+    cl = cl or ora.OracleCluster.from_snapshot(snap)
     probe = labels_fn(max(threads, 8))
     t0 = time.perf_counter()
     cl.eval(probe, faithful=faithful, threads=threads, full=False)
@@ -166,6 +166,10 @@ def main():
     ap.add_argument("--pods", type=int, default=0, help="override pods per batch")
     ap.add_argument("--mode", default="full", choices=["full", "decide"])
     ap.add_argument("--force-direct", action="store_true")
+    ap.add_argument("--shard", default="nodes", choices=["nodes", "pods"],
+                    help="N>1: nodes = each GPU owns a slice of the cluster, pods replicated, three small exchanges (BASELINE config 4); "
+                         "pods = snapshot replicated, each GPU takes its own pods, no exchange at all")
+    ap.add_argument("--round-values", action="store_true", help="pod variant with round scv/memory values (few requirement classes)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
     args = ap.parse_args()
@@ -187,14 +191,15 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    n_nodes, n_pods, pod_seed = workload(args, rank, world)   # per-GPU shard
-    node_base = rank * n_nodes
+    pod_sharded = args.shard == "pods" and world > 1
+    n_nodes, n_pods, pod_seed = workload(args, rank, 1 if pod_sharded else world)   # per-GPU shard
+    node_base = 0 if pod_sharded else rank * n_nodes
     snap = synth.make_snapshot(n_nodes, node_offset=node_base)
-    reqs_np = synth.make_requests(n_pods, pod_seed)
+    reqs_np = synth.make_requests(n_pods, pod_seed + (rank if pod_sharded else 0), args.round_values)
     flags = (api.EVAL_FULL if args.mode == "full" else api.EVAL_DECIDE) | (api.EVAL_FORCE_DIRECT if args.force_direct else 0)
 
-    ctx = api.Context(n_nodes, device=local_rank, node_base=node_base, shard_rank=rank, shard_count=world)
-    if world > 1:
+    ctx = api.Context(n_nodes, device=local_rank, node_base=node_base, shard_rank=0 if pod_sharded else rank, shard_count=1 if pod_sharded else world)
+    if world > 1 and not pod_sharded:
         idt = torch.zeros(128, dtype=torch.uint8, device=dev)
         if rank == 0:
             buf = np.zeros(128, np.uint8)
@@ -302,8 +307,9 @@ def main():
         tt = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms, e2e_ms = tt.tolist()
-    total_nodes = n_nodes * world
-    evals = float(n_pods) * total_nodes
+    total_nodes = n_nodes if pod_sharded else n_nodes * world
+    total_pods = n_pods * world if pod_sharded else n_pods
+    evals = float(total_pods) * total_nodes
     value = evals / (ms * 1e-3)
     e2e_value = evals / (e2e_ms * 1e-3)
 
@@ -319,9 +325,12 @@ def main():
         step_bytes = algorithmic_bytes(n_pods, n_nodes) if full else n_nodes * R_NODE + n_pods * (R_POD + R_OUT)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if args.config == "c4" else "weak", "vs_baseline": None, "dtype": "u64" if t_last.path == 0 else "u32",
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if (args.config == "c4" and not pod_sharded) else "weak", "vs_baseline": None, "dtype": "u64" if t_last.path == 0 else "u32",
             "data": "synthetic",
-            "config": {"workload": f"{args.config}: {n_nodes} nodes x 8 cards per GPU ({total_nodes} total, node-sharded), {n_pods} pods, mode={args.mode}",
+            "config": {"workload": (f"{args.config}: {n_nodes} nodes x 8 cards replicated on every GPU, {n_pods} pods per GPU ({total_pods} total, pod-sharded, no exchange), mode={args.mode}"
+                                    if pod_sharded else
+                                    f"{args.config}: {n_nodes} nodes x 8 cards per GPU ({total_nodes} total, node-sharded), {n_pods} pods, mode={args.mode}")
+                                   + (", round scv/memory values" if args.round_values else ""),
                        "l2": "every step writes the result matrices (>> 126 MB L2), which sweeps L2 between iterations; the snapshot is L2-resident by design",
                        "path": "narrow-fast" if t_last.path == 1 else "direct-u64", "classes": t_last.n_classes, "groups": t_last.n_groups},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(reqs_np.nbytes), "d2h_bytes_per_step": int(n_pods * api.POD_RES.itemsize)},
@@ -356,7 +365,7 @@ def main():
         if world == 1 and not args.no_latency:
             # p50/p99 batch latency at this snapshot size, host buffers in -> per-pod results out
             lat = {}
-            for pp, reps in ((1, 300), (1000, 300), (n_pods, 40)):
+            for pp, reps in ((1, 300), (1000, 300), (n_pods, 200)):
                 if pp > n_pods:
                     continue
                 sub = np.ascontiguousarray(reqs_np[:pp])
@@ -371,7 +380,7 @@ def main():
             line["latency"] = {"nodes": n_nodes, "mode": args.mode, **lat}
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            all_labels = synth.make_pod_labels(min(n_pods, 4096), pod_seed)
+            all_labels = synth.make_pod_labels(min(n_pods, 4096), pod_seed, args.round_values)
             labels_fn = lambda k: [all_labels[i % len(all_labels)] for i in range(k)]
             cl, sample, _ = cpu_arm(snap, labels_fn, n_nodes, cores, 12.0)
             t0 = time.perf_counter()
@@ -379,6 +388,17 @@ def main():
             dt = time.perf_counter() - t0
             line["cpu_baseline"] = {"value": sample * n_nodes / dt, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"{sample} pods x {n_nodes} nodes, oracle faithful driver, {cores} threads, {dt:.1f} s"}
+            # faithful (per-pair label lookup + Atoi + string compare + Scv copy) and lean drivers,
+            # one thread and min(16, cores) threads (16 = the framework's default parallelism); ~2 s each
+            variants = {}
+            for faithful in (True, False):
+                for th in sorted({1, min(16, cores)}):
+                    _, smp, _ = cpu_arm(snap, labels_fn, n_nodes, th, 2.0, faithful=faithful, cl=cl)
+                    t0 = time.perf_counter()
+                    cl.eval(labels_fn(smp), faithful=faithful, threads=th, full=False)
+                    d = time.perf_counter() - t0
+                    variants[f"{'faithful' if faithful else 'lean'}_{th}t"] = {"value": smp * n_nodes / d, "sample_pods": smp, "seconds": d}
+            line["cpu_baseline"]["variants"] = variants
         print(json.dumps(line))
     ctx.close()
     if world > 1:

@@ -100,3 +100,29 @@ def test_two_gpus_nccl(tmp_path):
         want = single.eval(synth.make_requests(P, 31), api.EVAL_FULL)
     for r in range(world):
         assert np.array_equal(np.load(tmp_path / f"res{r}.npy"), want)
+
+
+def test_pod_sharding_equals_single():
+    """The other way to use several GPUs (bench.py --shard pods): the snapshot is
+    replicated, every GPU takes its own slice of the pending pods, nothing is exchanged.  Two contexts
+    on cuda:0 stand in for two GPUs: their results, concatenated, are the single-batch results."""
+    N, P = 3000, 601
+    snap = synth.make_snapshot(N)
+    reqs = synth.make_requests(P, 77)
+    with api.Context(N) as single:
+        single.load_snapshot(snap)
+        want = single.eval(reqs, api.EVAL_FULL)
+        want_m = single.fetch_all(P)
+    cut = 300
+    got, rows = [], {"feasible": [], "raw": [], "norm": []}
+    for part in (reqs[:cut], reqs[cut:]):
+        with api.Context(N) as c:
+            c.load_snapshot(snap)
+            got.append(c.eval(np.ascontiguousarray(part), api.EVAL_FULL))
+            m = c.fetch_all(len(part))
+            for k in rows:
+                rows[k].append(m[k])
+    assert np.array_equal(np.concatenate(got), want)
+    for k in rows:
+        assert np.array_equal(np.concatenate(rows[k]), want_m[k]), k
+    assert_matches_oracle(snap, synth.make_pod_labels(P, 77), want, want_m, what="pod-sharded")
