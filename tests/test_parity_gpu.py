@@ -379,3 +379,27 @@ def test_context_reuse_across_batch_sizes_and_modes():
                         assert np.array_equal(rows[key], w[key]), (k, key)
                 if k == 3:
                     assert np.array_equal(seq, fresh.eval_sequential(all_reqs[:500]))
+
+
+@pytest.mark.parametrize("n_pods", [3, 40])
+def test_class_tables_plain_division_branches(n_pods):
+    """The class tables divide by multiplying with a reciprocal when 100*x fits 32 bits and the maximum
+    is at least 2; these nodes report memory in KB (fields above 2^32/100) and every bandwidth is 0 or 1
+    (MaxBandwidth == 1, so Clock*100/MaxBandwidth is Clock*100): both plain-division branches run, inside
+    the fast path, and must give the reference's quotients."""
+    rng = random.Random(5)
+    nodes = []
+    for i in range(90):
+        big = i % 3 != 0                      # every third node stays small: both kinds in one CTA
+        total = 3_000_000_000 + 1000 * i if big else 16_000 + i
+        cards = [{"health": "Healthy" if rng.random() > 0.1 else "Unhealthy", "free": rng.randrange(total + 1), "total": total,
+                  "clock": 1000 + 7 * i + g, "core": 5000 + i, "bandwidth": (i + g) % 2, "power": 300} for g in range(4)]
+        nodes.append({"name": f"n{i}", "has_scv": True, "card_number": 4, "free_sum": sum(c["free"] for c in cards),
+                      "total_sum": 4 * total, "pods": [], "cards": cards})
+    snap = Snapshot.from_nodes(nodes)
+    labels = [{"scv/memory": str(rng.choice([1, 9000, 40_000_000, 1_500_000_000, 2_900_000_000])), **({"scv/number": "2"} if k % 2 else {})}
+              for k in range(n_pods)]
+    labels[0] = {"scv/memory": "4000000000"}  # nothing fits: the all-ones class
+    res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_FULL)
+    assert t.path == 1, "these values are narrow: the table path must have handled them"
+    assert_matches_oracle(snap, labels, res, mats)

@@ -378,57 +378,108 @@ __global__ void k_class_assign(PodS *pods, u32 P, const u64 *__restrict__ max6, 
     }
 }
 
-// exact floor(x * 100 / d) for x, d < 2^32, d >= 1, with the divisor's reciprocal M = ceil(2^64 / d)
-// (M == 0 stands for d == 1): mulhi(a, M) == floor(a / d) for every a < 2^32, because M*d = 2^64 + e with
-// 0 <= e < d and a*e < 2^64; larger a divide for real
-__device__ __forceinline__ u32 div100(u32 x, u32 d, u64 M, bool &big) {
-    const u64 a = (u64)x * 100ull;
-    const u64 q = (a >> 32) ? a / (u64)d : (M ? __umul64hi(a, M) : a);
-    big |= q >= CS_LIMIT;
-    return (u32)q;
-}
-
 // Per class, per card: CalculateCardScore (algorithm.go:57-68) packed with the card's health bit.
 // A card whose fields exceed the class maxima can never be scored by a pod of that class (it would
 // have raised the maxima), so its score slot is 0; its health bit stays (Filter still counts it).
+//
+// floor(x * 100 / d) is taken with the divisor's reciprocal M = ceil(2^64 / d), d >= 2: for every
+// a = 100x < 2^32, mulhi64(a, M) == floor(a / d), because M*d = 2^64 + e with 0 <= e < d and a*e < 2^64.
+// With a in 32 bits that is one 32x32 high product and one 32x32+64 multiply-add.  Nodes with a field
+// >= 2^32/100 and classes with a maximum of 1 (no 64-bit reciprocal) take the plain-division path.
 #define CLST 128
+#define CLS_PER 4  // classes per thread: the node's 48 field values are loaded once and reused
+
+__device__ __forceinline__ u32 rdiv(u32 a, u32 Mhi, u32 Mlo) {
+    return (u32)(((u64)a * Mhi + __umulhi(a, Mlo)) >> 32);  // a*Mhi + carry < 2^64
+}
+
+// plain 64-bit arithmetic for one card; dm = the class maxima in cls_max order (bw, clock, core, free, power, total)
+// bit 31 of the result = "a term left the packed range"
+__device__ __forceinline__ u32 card_score_plain(const DevSnap &s, u32 n, int g, const u32 *dm) {
+    const size_t o = (size_t)n * G + g;
+    const u32 bw = s.n32[F_BW][o], ck = s.n32[F_CLOCK][o], co = s.n32[F_CORE][o], pw = s.n32[F_POWER][o], fr = s.n32[F_FREE][o],
+              to = s.n32[F_TOTAL][o];
+    if (!(bw <= dm[0] && ck <= dm[1] && co <= dm[2] && fr <= dm[3] && pw <= dm[4] && to <= dm[5])) return 0;
+    const u64 q0 = (u64)bw * 100ull / dm[0], q1 = (u64)ck * 100ull / dm[0], q2 = (u64)co * 100ull / dm[2], q3 = (u64)pw * 100ull / dm[4],
+              q4 = (u64)fr * 100ull / dm[3], q5 = (u64)to * 100ull / dm[5];
+    const u64 cs = q0 + q1 + q2 + q3 + q4 * 2ull + q5;  // every term < 2^39
+    return ((u32)cs & CS_SCORE_MASK) | (((q0 | q1 | q2 | q3 | q4 | q5 | cs) >= CS_LIMIT) ? 0x80000000u : 0u);
+}
+
+struct ClassConsts {
+    u32 d[6];     // maxima in cls_max order
+    u32 d100[6];  // min(100 * d, 2^32 - 1): a <= d100 <=> x <= d for every a = 100x < 2^32
+    u32 mhi[6], mlo[6];
+    u32 plain;    // some maximum is 1
+};
+
 __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__restrict__ cls_max, u32 n_classes, u32 *tables,
                                                        FastCtl *ctl) {
-    __shared__ u64 magic[6];
-    const u32 cid = blockIdx.y;
-    if (cid >= n_classes) return;
-    if (threadIdx.x < 6) {
-        const u32 d = cls_max[cid * 6 + threadIdx.x];
-        magic[threadIdx.x] = d > 1 ? (0xFFFFFFFFFFFFFFFFull / d) + 1ull : 0ull;  // ceil(2^64 / d), also for powers of two
+    __shared__ ClassConsts cc[CLS_PER];
+    const u32 cid0 = blockIdx.y * CLS_PER;
+    if (cid0 >= n_classes) return;
+    const u32 ncls = min((u32)CLS_PER, n_classes - cid0);
+    if (threadIdx.x < CLS_PER) cc[threadIdx.x].plain = 0;
+    __syncthreads();
+    if (threadIdx.x < ncls * 6) {
+        const u32 k = threadIdx.x / 6, f = threadIdx.x % 6;
+        const u32 d = cls_max[cid0 * 6 + threadIdx.x];
+        const u64 M = d > 1 ? (0xFFFFFFFFFFFFFFFFull / d) + 1ull : 0ull;  // ceil(2^64 / d), also for powers of two
+        cc[k].d[f] = d;
+        cc[k].d100[f] = (u32)min((u64)d * 100ull, 0xFFFFFFFFull);
+        cc[k].mhi[f] = (u32)(M >> 32);
+        cc[k].mlo[f] = (u32)M;
+        if (d <= 1) cc[k].plain = 1;
     }
     __syncthreads();
     const u32 n = blockIdx.x * CLST + threadIdx.x;
     if (n >= s.n_nodes) return;
-    const u32 mbw = cls_max[cid * 6 + 0], mck = cls_max[cid * 6 + 1], mco = cls_max[cid * 6 + 2], mfr = cls_max[cid * 6 + 3],
-              mpw = cls_max[cid * 6 + 4], mto = cls_max[cid * 6 + 5];
-    const u64 Mbw = magic[0], Mco = magic[2], Mfr = magic[3], Mpw = magic[4], Mto = magic[5];
     const u32 hm = meta_healthy(s.meta[n]);
-    u32 out[G];
-    bool big = false;
+    // a node's eight values of one field are 32 contiguous bytes: two 16-byte loads per field; kept as 100x
+    u32 a[6][G];
+    bool node_plain = false;
 #pragma unroll
-    for (int g = 0; g < G; ++g) {
-        const size_t o = (size_t)n * G + g;
-        const u32 bw = s.n32[F_BW][o], ck = s.n32[F_CLOCK][o], co = s.n32[F_CORE][o], pw = s.n32[F_POWER][o], fr = s.n32[F_FREE][o],
-                  to = s.n32[F_TOTAL][o];
-        u32 cs = 0;
-        if (bw <= mbw && ck <= mck && co <= mco && pw <= mpw && fr <= mfr && to <= mto) {
-            bool b = false;
-            cs = div100(bw, mbw, Mbw, b) + div100(ck, mbw, Mbw, b) + div100(co, mco, Mco, b) + div100(pw, mpw, Mpw, b) +
-                 div100(fr, mfr, Mfr, b) * 2u + div100(to, mto, Mto, b);
-            b |= cs >= CS_LIMIT;
-            big |= b;
-            cs &= CS_SCORE_MASK;
+    for (int f = 0; f < 6; ++f) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(s.n32[f] + (size_t)n * G);
+        const uint4 v0 = src[0], v1 = src[1];
+        const u32 v[G] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            node_plain |= v[g] > 0xFFFFFFFFu / 100u;
+            a[f][g] = v[g] * 100u;
         }
-        out[g] = cs | (((hm >> g) & 1u) << CS_HEALTH_SHIFT);
     }
-    uint4 *dst = reinterpret_cast<uint4 *>(tables + ((size_t)cid * s.cap + n) * G);
-    dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
-    dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
+    bool big = false;
+    for (u32 k = 0; k < ncls; ++k) {
+        const ClassConsts &c = cc[k];
+        u32 out[G];
+        if (node_plain || c.plain) {
+#pragma unroll 1
+            for (int g = 0; g < G; ++g) {
+                const u32 cs = card_score_plain(s, n, g, c.d);
+                big |= (cs >> 31) != 0;
+                const u32 w = (cs & CS_SCORE_MASK) | (((hm >> g) & 1u) << CS_HEALTH_SHIFT);
+#pragma unroll
+                for (int h = 0; h < G; ++h)
+                    if (h == g) out[h] = w;
+            }
+        } else {
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                const bool adm = a[F_BW][g] <= c.d100[0] && a[F_CLOCK][g] <= c.d100[1] && a[F_CORE][g] <= c.d100[2] &&
+                                 a[F_FREE][g] <= c.d100[3] && a[F_POWER][g] <= c.d100[4] && a[F_TOTAL][g] <= c.d100[5];
+                const u32 q0 = rdiv(a[F_BW][g], c.mhi[0], c.mlo[0]), q1 = rdiv(a[F_CLOCK][g], c.mhi[0], c.mlo[0]),
+                          q2 = rdiv(a[F_CORE][g], c.mhi[2], c.mlo[2]), q3 = rdiv(a[F_POWER][g], c.mhi[4], c.mlo[4]),
+                          q4 = rdiv(a[F_FREE][g], c.mhi[3], c.mlo[3]), q5 = rdiv(a[F_TOTAL][g], c.mhi[5], c.mlo[5]);
+                const u32 cs = q0 + q1 + q2 + q3 + q4 * 2u + q5;  // exact when every term < CS_LIMIT, flagged otherwise
+                big |= adm && ((q0 | q1 | q2 | q3 | q4 | q5 | cs) >= CS_LIMIT);
+                out[g] = (adm ? (cs & CS_SCORE_MASK) : 0u) | (((hm >> g) & 1u) << CS_HEALTH_SHIFT);
+            }
+        }
+        uint4 *dst = reinterpret_cast<uint4 *>(tables + ((size_t)(cid0 + k) * s.cap + n) * G);
+        dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
+        dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
+    }
     if (big) atomicOr(&ctl->err, FAST_ERR_WIDE_CLASS);
 }
 

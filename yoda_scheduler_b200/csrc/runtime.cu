@@ -693,7 +693,7 @@ static int fast_classes(yoda_ctx *c) {
             c->fw_tables_classes = want;
         }
         if (N) {
-            k_class_tables<<<dim3((N + CLST - 1) / CLST, P), CLST, 0, st>>>(c->snap, c->fw_cls_max, P, c->fw_tables, c->fw_ctl);
+            k_class_tables<<<dim3((N + CLST - 1) / CLST, (P + CLS_PER - 1) / CLS_PER), CLST, 0, st>>>(c->snap, c->fw_cls_max, P, c->fw_tables, c->fw_ctl);
             LAUNCHED(c);
         }
         if (c->fw_allow_defer) {
@@ -737,7 +737,7 @@ static int fast_classes(yoda_ctx *c) {
         c->fw_tables_classes = want;
     }
     if (N) {
-        dim3 grid((N + CLST - 1) / CLST, c->fw_n_classes);
+        dim3 grid((N + CLST - 1) / CLST, (c->fw_n_classes + CLS_PER - 1) / CLS_PER);
         k_class_tables<<<grid, CLST, 0, st>>>(c->snap, c->fw_cls_max, c->fw_n_classes, c->fw_tables, c->fw_ctl);
         LAUNCHED(c);
     }
