@@ -37,6 +37,10 @@ struct DevSnap {
     u32 *n32[NFIELD];   // [cap][G] uint32 copies of the card planes
     u32 *cardnum32;     // [cap]
     u32 *stat32;        // [cap]
+    // nodes ordered by the Clock of their first card (nodes without an SCV last): neighbouring lanes then agree on
+    // an scv/clock test, so the per-group work of the maxima pass is warp-uniform.  Rebuilt at commit when a key changed.
+    u32 *order;         // [cap] permutation of 0..n_nodes-1
+    u32 *order_key;     // [cap] the key each node was last ordered by
     u32 n_nodes;        // committed node count (highest index + 1)
     u32 cap;
     u32 node_base;      // global index of local node 0

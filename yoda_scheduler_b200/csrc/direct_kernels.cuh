@@ -47,7 +47,8 @@ __global__ void k_scatter_updates(DevSnap s, const UpdRec *__restrict__ upd, u32
 //   stat[n]  = CalculateAllocateScore + CalculateActualScore  (algorithm.go:70-87), wrapping u64
 //   narrow planes + the snapshot-wide "narrow eligible" verdict:
 //     every card field < 2^32-1, CardNumber < 2^32-1, stat < 2^24.
-// wide_flag[0] is set to 1 if any node with an SCV falls outside the narrow range.
+// wide_flag[0] is set to 1 if any node with an SCV falls outside the narrow range,
+// wide_flag[1] if a node's ordering key (see DevSnap::order) changed.
 #define NARROW_FIELD_LIMIT 0xFFFFFFFFull  /* exclusive */
 #define NARROW_STAT_LIMIT (1ull << 24)    /* exclusive */
 __global__ void k_prepare(DevSnap s, u32 *wide_flag) {
@@ -80,6 +81,16 @@ __global__ void k_prepare(DevSnap s, u32 *wide_flag) {
         for (int f = 0; f < NFIELD; ++f) s.n32[f][o] = (u32)s.f[f][o];
     }
     if (wide) atomicOr(wide_flag, 1u);
+    const u32 key = (meta & META_HAS_SCV) ? min((u32)s.f[F_CLOCK][(size_t)n * G], 0xFFFFFFFDu) : 0xFFFFFFFEu;
+    if (s.order_key[n] != key) {
+        s.order_key[n] = key;
+        wide_flag[1] = 1u;
+    }
+}
+
+__global__ void k_iota(u32 *v, u32 n) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] = i;
 }
 
 // ------------------------------------------------------------------------------------------

@@ -216,9 +216,9 @@ __global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupD
     __shared__ GroupDesc sg[MAXG_TILE];
     const u32 n_groups = group_count(ctl, n_groups_host);
     if (blockIdx.y * MAXG_TILE >= n_groups) return;
-    const u32 n = blockIdx.x * MAXT + threadIdx.x;
-    const bool live = n < s.n_nodes;
-    const u32 nn = live ? n : 0;
+    const u32 slot = blockIdx.x * MAXT + threadIdx.x;
+    const bool live = slot < s.n_nodes;
+    const u32 nn = live ? s.order[slot] : 0;  // nodes with the same clock sit in the same warps
     const u32 meta = live ? s.meta[nn] : 0u;
     const bool has = (meta & META_HAS_SCV) != 0;
     const u32 nc = meta_ncards(meta), hm = meta_healthy(meta);
@@ -270,19 +270,27 @@ __global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupD
             }
             const u32 *ms = m_sorted + gd.seg_start;
             const u32 len = gd.seg_end - gd.seg_start;
+            if (!len) continue;
+            // j[g] = number of pods of the group with memory <= e[g], for the eight cards at once: a branch-free
+            // upper bound with the same trip count for every card, so eight independent loads are in flight per step
+            u32 e[G], j[G];
 #pragma unroll
             for (int g = 0; g < G; ++g) {
-                if (g >= (int)nc || ck[g] < gd.c) continue;  // collection.go:46 (clock >= c; c == 0 without the label)
-                const u32 e = min(fr[g], T);
-                // j = number of pods of the group with memory <= e
-                u32 lo = 0, hi = len;
-                while (lo < hi) {
-                    const u32 mid = (lo + hi) >> 1;
-                    if (ms[mid] <= e) lo = mid + 1; else hi = mid;
-                }
-                if (lo == 0) continue;
-                const u32 pos = gd.seg_start + lo - 1;
-                const size_t o = (size_t)n * G + g;
+                e[g] = min(fr[g], T);
+                j[g] = 0;
+            }
+            for (u32 rem = len; rem > 1;) {
+                const u32 half = rem >> 1;
+#pragma unroll
+                for (int g = 0; g < G; ++g) j[g] += (ms[j[g] + half - 1] <= e[g]) ? half : 0u;
+                rem -= half;
+            }
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                j[g] += (ms[j[g]] <= e[g]) ? 1u : 0u;
+                if (g >= (int)nc || ck[g] < gd.c || j[g] == 0) continue;  // collection.go:46 (clock >= c; c == 0 without the label)
+                const u32 pos = gd.seg_start + j[g] - 1;
+                const size_t o = (size_t)nn * G + g;
                 // collection.go:59-78; order of the step planes = collection.MaxValue (bw, clock, core, free, power, total)
                 const u32 v[6] = {s.n32[F_BW][o], ck[g], s.n32[F_CORE][o], fr[g], s.n32[F_POWER][o], s.n32[F_TOTAL][o]};
 #pragma unroll

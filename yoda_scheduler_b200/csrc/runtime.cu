@@ -94,7 +94,11 @@ struct yoda_ctx {
     yoda_config cfg{};
     cudaStream_t own_stream = nullptr, stream = nullptr;
     DevSnap snap{};
-    u32 *d_wide_flag = nullptr;
+    u32 *d_wide_flag = nullptr;  // [2]: snapshot outside the narrow range, node ordering keys changed
+    u32 *ord_keys_out = nullptr, *ord_iota = nullptr;  // scratch of the node ordering sort
+    void *ord_tmp = nullptr;
+    size_t ord_tmp_bytes = 0;
+    u32 ord_nodes = 0;           // node count the current DevSnap::order was built for
     bool narrow_ok = false;
     uint64_t epoch = 0;
     // update staging
@@ -237,7 +241,17 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
     for (int f = 0; f < NFIELD && !rc; ++f) rc = dev_alloc(&s.n32[f], (size_t)cap * G);
     if (!rc) rc = dev_alloc(&s.cardnum32, cap);
     if (!rc) rc = dev_alloc(&s.stat32, cap);
-    if (!rc) rc = dev_alloc(&c->d_wide_flag, 1);
+    if (!rc) rc = dev_alloc(&c->d_wide_flag, 2);
+    if (!rc) rc = dev_alloc(&s.order, cap);
+    if (!rc) rc = dev_alloc(&s.order_key, cap);
+    if (!rc) rc = dev_alloc(&c->ord_keys_out, cap);
+    if (!rc) rc = dev_alloc(&c->ord_iota, cap);
+    if (!rc) {
+        if (cub::DeviceRadixSort::SortPairs(nullptr, c->ord_tmp_bytes, s.order_key, c->ord_keys_out, c->ord_iota, s.order, (int)cap, 0, 32,
+                                            c->stream) != cudaSuccess ||
+            cudaMalloc(&c->ord_tmp, std::max<size_t>(c->ord_tmp_bytes, 16)) != cudaSuccess)
+            rc = fail(YODA_E_NOMEM, "scratch of the node ordering sort");
+    }
     if (!rc) rc = dev_alloc(&c->d_lohi, 2);
     if (rc) return bail(rc);
     for (int f = 0; f < NFIELD; ++f) cudaMemsetAsync(s.f[f], 0, (size_t)cap * G * 8, c->stream);
@@ -247,6 +261,7 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
     cudaMemsetAsync(s.alloc_sum, 0, (size_t)cap * 8, c->stream);
     cudaMemsetAsync(s.stat, 0, (size_t)cap * 8, c->stream);
     cudaMemsetAsync(s.meta, 0, (size_t)cap * 4, c->stream);
+    cudaMemsetAsync(s.order_key, 0xFF, (size_t)cap * 4, c->stream);  // no node has this key: the first commit orders
     c->upd_cap = std::min<u32>(cfg->max_nodes, 1u << 16);
     if (cudaMallocHost((void **)&c->h_upd, (size_t)c->upd_cap * sizeof(UpdRec)) != cudaSuccess)
         return bail(fail(YODA_E_NOMEM, "cudaMallocHost of the update staging buffer failed"));
@@ -268,7 +283,9 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     dev_free(s.card_number); dev_free(s.free_sum); dev_free(s.total_sum); dev_free(s.alloc_sum);
     dev_free(s.stat); dev_free(s.meta);
     for (int f = 0; f < NFIELD; ++f) dev_free(s.n32[f]);
-    dev_free(s.cardnum32); dev_free(s.stat32);
+    dev_free(s.cardnum32); dev_free(s.stat32); dev_free(s.order); dev_free(s.order_key);
+    dev_free(c->ord_keys_out); dev_free(c->ord_iota);
+    if (c->ord_tmp) cudaFree(c->ord_tmp);
     dev_free(c->d_wide_flag); dev_free(c->d_lohi); dev_free(c->d_list); dev_free(c->d_upd);
     dev_free(c->d_req); dev_free(c->d_pods); dev_free(c->d_max6); dev_free(c->d_count);
     dev_free(c->d_hilo); dev_free(c->d_ckey); dev_free(c->d_res);
@@ -406,15 +423,24 @@ extern "C" int yoda_commit(yoda_ctx *c, uint64_t *epoch) {
     TRY(flush_updates(c));
     c->snap.n_nodes = c->n_nodes_pending;
     c->flushed_uncommitted = false;
-    CU(cudaMemsetAsync(c->d_wide_flag, 0, sizeof(u32), c->stream));
-    if (c->snap.n_nodes) {
-        k_prepare<<<(c->snap.n_nodes + 255) / 256, 256, 0, c->stream>>>(c->snap, c->d_wide_flag);
+    CU(cudaMemsetAsync(c->d_wide_flag, 0, 2 * sizeof(u32), c->stream));
+    const u32 N = c->snap.n_nodes;
+    if (N) {
+        k_prepare<<<(N + 255) / 256, 256, 0, c->stream>>>(c->snap, c->d_wide_flag);
         CU(cudaGetLastError());
     }
-    u32 wide = 0;
-    CU(cudaMemcpyAsync(&wide, c->d_wide_flag, sizeof(u32), cudaMemcpyDeviceToHost, c->stream));
+    u32 flag[2] = {0, 0};
+    CU(cudaMemcpyAsync(flag, c->d_wide_flag, sizeof flag, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    c->narrow_ok = (wide == 0);
+    c->narrow_ok = (flag[0] == 0);
+    if (N && (flag[1] || N != c->ord_nodes)) {  // metric ticks that leave the clocks alone keep the order
+        k_iota<<<(N + 255) / 256, 256, 0, c->stream>>>(c->ord_iota, N);
+        CU(cudaGetLastError());
+        size_t bytes = c->ord_tmp_bytes;
+        CU(cub::DeviceRadixSort::SortPairs(c->ord_tmp, bytes, c->snap.order_key, c->ord_keys_out, c->ord_iota, c->snap.order, (int)N, 0, 32,
+                                           c->stream));
+        c->ord_nodes = N;
+    }
     c->epoch++;
     c->last_P = 0;  // result matrices belong to the previous snapshot
     if (epoch) *epoch = c->epoch;
