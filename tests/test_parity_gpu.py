@@ -403,3 +403,25 @@ def test_class_tables_plain_division_branches(n_pods):
     res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_FULL)
     assert t.path == 1, "these values are narrow: the table path must have handled them"
     assert_matches_oracle(snap, labels, res, mats)
+
+
+def test_maxima_scan_across_tiles():
+    """Requirement groups much longer than one scan tile (1024 pods), groups that start and end inside a
+    tile, and a tail of one-pod groups: the maxima of every pod against the oracle."""
+    rng = random.Random(11)
+    N, P = 300, 5000
+    snap = synth.make_snapshot(N)
+    labels = []
+    for k in range(P):
+        r = rng.random()
+        if r < 0.70:
+            labels.append({"scv/memory": str(rng.randrange(1, 90000))})                       # one group of ~3500 pods
+        elif r < 0.90:
+            labels.append({"scv/memory": str(rng.randrange(1, 90000)), "scv/number": "2"})    # ~1000
+        elif r < 0.98:
+            labels.append({"scv/number": str(rng.choice([1, 4]))})                            # no memory: all equal inside the group
+        else:
+            labels.append({"scv/clock": str(1000 + k), "scv/memory": str(rng.randrange(1, 90000))})  # ~100 groups of one pod
+    res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_DECIDE, fetch=False)
+    assert t.path == 1 and t.n_groups > 50
+    assert_matches_oracle(snap, labels, res, None)

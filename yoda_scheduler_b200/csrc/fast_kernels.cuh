@@ -301,46 +301,71 @@ __global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupD
     }
 }
 
-// one CTA per (group, field): suffix maximum over the group's pod segment, result max(1, .) into max6[orig]
+// Suffix maxima of the step planes over every group's pod segment, result max(1, .) into max6[orig].
+// Positions are cut into tiles of SCANT regardless of the groups, so one huge group costs no more than
+// many small ones.  k_max_tile_lead: per (tile, field) the maximum over the tile's leading run of positions
+// that belong to the group of its first position -- what the tiles before it need.  k_max_scan: a segmented
+// suffix scan inside the tile (groups are contiguous; a position's run ends at its group's seg_end), plus,
+// for the group of the tile's last position, the leads of the later tiles that start inside that group.
 #define SCANT 1024
-__global__ void __launch_bounds__(SCANT) k_max_scan(const GroupDesc *__restrict__ gdesc, u32 n_groups_host, const FastCtl *__restrict__ ctl,
-                                                    const u32 *__restrict__ step, const PodS *__restrict__ pods, u64 *max6, u32 P) {
+__global__ void __launch_bounds__(SCANT) k_max_tile_lead(const GroupDesc *__restrict__ gdesc, const u32 *__restrict__ step,
+                                                         const PodS *__restrict__ pods, u32 *lead, u32 P, u32 n_tiles) {
     __shared__ u32 warp_max[SCANT / 32];
-    __shared__ u32 carry_s;
-    const u32 n_groups = group_count(ctl, n_groups_host);
-    const u32 f = blockIdx.y;
-    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const u32 *sf = step + (size_t)f * P;
-    for (u32 gid = blockIdx.x; gid < n_groups; gid += gridDim.x) {
-        const GroupDesc gd = gdesc[gid];
-        __syncthreads();
-        if (threadIdx.x == 0) carry_s = 0;
-        __syncthreads();
-        // walk the segment backwards in tiles of SCANT; thread t handles position top-1-t of the tile
-        for (u32 top = gd.seg_end; top > gd.seg_start;) {
-            const u32 cnt = min(SCANT, top - gd.seg_start);
-            const bool live = threadIdx.x < cnt;
-            const u32 pos = live ? top - 1 - threadIdx.x : 0;
-            u32 v = live ? sf[pos] : 0u;
-            // inclusive prefix max over threadIdx (= suffix max over positions)
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const u32 t = __shfl_up_sync(0xFFFFFFFFu, v, o);
-                if (lane >= (u32)o) v = max(v, t);
-            }
-            if (lane == 31) warp_max[warp] = v;
-            __syncthreads();
-            u32 pre = carry_s;
-            for (u32 w = lane; w < warp; w += 32) pre = max(pre, warp_max[w]);
-            pre = __reduce_max_sync(0xFFFFFFFFu, pre);
-            v = max(v, pre);
-            if (live) max6[(size_t)pods[pos].orig * 6 + f] = (u64)max(v, 1u);  // collection.go:31-38
-            __syncthreads();
-            if (threadIdx.x == SCANT - 1) carry_s = v;
-            __syncthreads();
-            top -= cnt;
-        }
+    const u32 tile = blockIdx.x, f = blockIdx.y;
+    const u32 t0 = tile * SCANT, pos = t0 + threadIdx.x;
+    const u32 run_end = min(min(P, t0 + SCANT), gdesc[pods[t0].gid].seg_end);
+    u32 v = pos < run_end ? step[(size_t)f * P + pos] : 0u;
+    v = __reduce_max_sync(0xFFFFFFFFu, v);
+    if ((threadIdx.x & 31) == 0) warp_max[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        v = __reduce_max_sync(0xFFFFFFFFu, warp_max[threadIdx.x]);
+        if (threadIdx.x == 0) lead[(size_t)f * n_tiles + tile] = v;
     }
+}
+
+__global__ void __launch_bounds__(SCANT) k_max_scan(const GroupDesc *__restrict__ gdesc, const u32 *__restrict__ step,
+                                                    const PodS *__restrict__ pods, const u32 *__restrict__ lead, u64 *max6, u32 P,
+                                                    u32 n_tiles) {
+    __shared__ u32 warp_lead[SCANT / 32];  // per warp: the run of its first position, as far as it goes inside the warp
+    __shared__ u32 red[SCANT / 32];
+    const u32 tile = blockIdx.x, f = blockIdx.y;
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u32 t0 = tile * SCANT, t1 = min(P, t0 + SCANT), pos = t0 + threadIdx.x;
+    const bool live = pos < t1;
+    const uint4 hi = live ? reinterpret_cast<const uint4 *>(pods + pos)[1] : make_uint4(0, 0, 0xFFFFFFFFu, 0);  // cls, orig, gid, pad
+    const u32 gid = hi.z, orig = hi.y;
+    u32 v = live ? step[(size_t)f * P + pos] : 0u;
+    // inside the warp: suffix maximum over the lanes after this one that are in the same group
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const u32 tv = __shfl_down_sync(0xFFFFFFFFu, v, o), tg = __shfl_down_sync(0xFFFFFFFFu, gid, o);
+        if (lane + o < 32 && tg == gid) v = max(v, tv);
+    }
+    if (lane == 0) warp_lead[warp] = v;
+    // the group of the tile's last position may go on in later tiles
+    const u32 g_tail = pods[t1 - 1].gid;
+    const u32 tail_end = gdesc[g_tail].seg_end;
+    u32 carry = 0;
+    for (u32 t = tile + 1 + threadIdx.x; t < n_tiles && t * SCANT < tail_end; t += SCANT) carry = max(carry, lead[(size_t)f * n_tiles + t]);
+    carry = __reduce_max_sync(0xFFFFFFFFu, carry);
+    if (lane == 0) red[warp] = carry;
+    __syncthreads();
+    // later warps of this tile that start inside the group of this warp's last lane
+    const u32 g_last = __shfl_sync(0xFFFFFFFFu, gid, 31);
+    const u32 last_end = g_last == 0xFFFFFFFFu ? 0u : gdesc[g_last].seg_end;
+    u32 pre = (lane > warp && t0 + lane * 32 < min(last_end, t1)) ? warp_lead[lane] : 0u;  // SCANT / 32 == 32 warps: one per lane
+    pre = __reduce_max_sync(0xFFFFFFFFu, pre);
+    carry = __reduce_max_sync(0xFFFFFFFFu, red[lane]);
+    if (gid == g_last) v = max(v, pre);
+    if (gid == g_tail) v = max(v, carry);
+    if (live) max6[(size_t)orig * 6 + f] = (u64)max(v, 1u);  // collection.go:31-38: the maxima start at 1
+}
+
+// small batches (k_small_groups): every pod is its own group, so its maxima are its own step entries
+__global__ void k_small_max_out(const u32 *__restrict__ step, const PodS *__restrict__ pods, u64 *max6, u32 P) {
+    const u32 i = threadIdx.x / 6, f = threadIdx.x % 6;
+    if (i < P) max6[(size_t)pods[i].orig * 6 + f] = (u64)max(step[(size_t)f * P + i], 1u);  // collection.go:31-38
 }
 
 // ------------------------------------------------------------------------------------------

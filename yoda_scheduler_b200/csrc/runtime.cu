@@ -144,6 +144,7 @@ struct yoda_ctx {
     size_t fw_cub_bytes = 0;
     GroupDesc *fw_gdesc = nullptr;
     PodS *fw_pods = nullptr;
+    u32 *fw_lead = nullptr;  // [6][tiles of SCANT pods] leading-run maxima of the maxima scan
     u32 *fw_m_sorted = nullptr, *fw_step = nullptr, *fw_cls_max = nullptr, *fw_tables = nullptr;
     u32 fw_tables_classes = 0;
     FastCtl *fw_ctl = nullptr, *fw_hctl = nullptr;
@@ -293,6 +294,7 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     dev_free(c->fw_gkeys); dev_free(c->fw_ckeys); dev_free(c->fw_gids); dev_free(c->fw_cids); dev_free(c->fw_crep);
     dev_free(c->fw_slot); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
     dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_gdesc); dev_free(c->fw_pods);
+    dev_free(c->fw_lead);
     dev_free(c->fw_m_sorted); dev_free(c->fw_step); dev_free(c->fw_cls_max); dev_free(c->fw_tables); dev_free(c->fw_ctl);
     dev_free(c->sq_alloc); dev_free(c->sq_stat); dev_free(c->sq_pos); dev_free(c->sq_order); dev_free(c->sq_status);
     if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
@@ -530,7 +532,7 @@ static int ensure_fast(yoda_ctx *c, u32 P) {
     dev_free(c->fw_gkeys); dev_free(c->fw_ckeys); dev_free(c->fw_gids); dev_free(c->fw_cids); dev_free(c->fw_crep);
     dev_free(c->fw_slot); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
     dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_pods);
-    dev_free(c->fw_m_sorted); dev_free(c->fw_step);
+    dev_free(c->fw_m_sorted); dev_free(c->fw_step); dev_free(c->fw_lead);
     if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
     c->fw_cub_tmp = nullptr;
     c->fw_pods_cap = 0;
@@ -547,6 +549,7 @@ static int ensure_fast(yoda_ctx *c, u32 P) {
     TRY(dev_alloc(&c->fw_pods, cap));
     TRY(dev_alloc(&c->fw_m_sorted, cap));
     TRY(dev_alloc(&c->fw_step, (size_t)cap * 6));
+    TRY(dev_alloc(&c->fw_lead, ((size_t)cap / SCANT + 1) * 6));
     size_t bytes = 0;
     CU(cub::DeviceRadixSort::SortPairs(nullptr, bytes, c->fw_keys_in, c->fw_keys_out, c->fw_vals_in, c->fw_vals_out, (int)cap, 0,
                                        33 + FAST_GID_BITS, c->stream));
@@ -603,6 +606,16 @@ static int direct_out_launch(yoda_ctx *c) {
 
 // ---- fast path bodies -------------------------------------------------------------------------
 // groups -> sorted pods -> maxima.  Returns with ph_path = 0 if the batch has too many groups.
+// step planes -> per-pod maxima (two launches, see k_max_scan)
+static int max_scan_launch(yoda_ctx *c, u32 P) {
+    const u32 n_tiles = (P + SCANT - 1) / SCANT;
+    k_max_tile_lead<<<dim3(n_tiles, 6), SCANT, 0, c->stream>>>(c->fw_gdesc, c->fw_step, c->fw_pods, c->fw_lead, P, n_tiles);
+    LAUNCHED(c);
+    k_max_scan<<<dim3(n_tiles, 6), SCANT, 0, c->stream>>>(c->fw_gdesc, c->fw_step, c->fw_pods, c->fw_lead, c->d_max6, P, n_tiles);
+    LAUNCHED(c);
+    return YODA_OK;
+}
+
 static int fast_phase0(yoda_ctx *c) {
     const u32 P = c->ph_P, N = c->snap.n_nodes;
     cudaStream_t st = c->stream;
@@ -619,7 +632,7 @@ static int fast_phase0(yoda_ctx *c) {
             k_max_thresholds<<<dim3((N + MAXT - 1) / MAXT, 1), MAXT, 0, st>>>(c->snap, c->fw_gdesc, P, nullptr, c->fw_m_sorted, c->fw_step, P);
             LAUNCHED(c);
         }
-        k_max_scan<<<dim3(P, 6), SCANT, 0, st>>>(c->fw_gdesc, P, nullptr, c->fw_step, c->fw_pods, c->d_max6, P);
+        k_small_max_out<<<1, FAST_SMALL_P * 6, 0, st>>>(c->fw_step, c->fw_pods, c->d_max6, P);
         LAUNCHED(c);
         return YODA_OK;
     }
@@ -657,13 +670,12 @@ static int fast_phase0(yoda_ctx *c) {
     CU(cudaEventRecord(c->ev[EV_PREP], st));
     CU(cudaMemsetAsync(c->fw_step, 0, (size_t)P * 6 * sizeof(u32), st));
     if (N) {
+        // eight groups per CTA pass: the per-node setup (loads, k-th largest FreeMemory) costs about as much as one group
         const dim3 grid((N + MAXT - 1) / MAXT, std::max(1u, std::min(32u, (groups_bound + MAXG_TILE - 1) / MAXG_TILE)));
         k_max_thresholds<<<grid, MAXT, 0, st>>>(c->snap, c->fw_gdesc, groups_bound, dctl, c->fw_m_sorted, c->fw_step, P);
         LAUNCHED(c);
     }
-    k_max_scan<<<dim3(std::max(1u, std::min(groups_bound, 2u * (u32)c->n_sms)), 6), SCANT, 0, st>>>(c->fw_gdesc, groups_bound, dctl, c->fw_step,
-                                                                                                   c->fw_pods, c->d_max6, P);
-    LAUNCHED(c);
+    TRY(max_scan_launch(c, P));
     c->fw_groups_pending = count_on_device;
     return YODA_OK;
 }
