@@ -20,6 +20,9 @@ typedef uint8_t u8;
 
 // node meta word: bits 0-7 healthy mask, bits 8-11 n_cards, bit 16 has_scv
 #define META_HAS_SCV 0x10000u
+// bits 24-31 (derived at commit): cards that no other card of the node dominates in all six fields -- the only ones
+// CollectMaxValues can ever take a maximum from
+__host__ __device__ __forceinline__ u32 meta_keep(u32 m) { return m >> 24; }
 __host__ __device__ __forceinline__ u32 meta_healthy(u32 m) { return m & 0xFFu; }
 __host__ __device__ __forceinline__ u32 meta_ncards(u32 m) { return (m >> 8) & 0xFu; }
 
@@ -37,6 +40,7 @@ struct DevSnap {
     u32 *n32[NFIELD];   // [cap][G] uint32 copies of the card planes
     u32 *cardnum32;     // [cap]
     u32 *stat32;        // [cap]
+    u32 *tk32;          // [cap][G] tk32[n][k] = (k+1)-th largest FreeMemory among the healthy cards (0 if fewer)
     // nodes ordered by the Clock of their first card (nodes without an SCV last): neighbouring lanes then agree on
     // an scv/clock test, so the per-group work of the maxima pass is warp-uniform.  Rebuilt at commit when a key changed.
     u32 *order;         // [cap] permutation of 0..n_nodes-1

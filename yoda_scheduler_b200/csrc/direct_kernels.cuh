@@ -81,6 +81,45 @@ __global__ void k_prepare(DevSnap s, u32 *wide_flag) {
         for (int f = 0; f < NFIELD; ++f) s.n32[f][o] = (u32)s.f[f][o];
     }
     if (wide) atomicOr(wide_flag, 1u);
+    // cards worth visiting for the maxima, and the k-th largest FreeMemory of the healthy cards
+    {
+        const u32 nc = meta_ncards(meta), hm = meta_healthy(meta);
+        u64 v[NFIELD][G];
+#pragma unroll
+        for (int f = 0; f < NFIELD; ++f)
+#pragma unroll
+            for (int g = 0; g < G; ++g) v[f][g] = s.f[f][(size_t)n * G + g];
+        u32 keep = 0, tk[G];
+#pragma unroll
+        for (int k = 0; k < G; ++k) tk[k] = 0;
+#pragma unroll
+        for (int b = 0; b < G; ++b) {
+            bool dominated = b >= (int)nc;
+            u32 rank = 0;
+#pragma unroll
+            for (int a = 0; a < G; ++a) {
+                if (a == b) continue;
+                bool ge = a < (int)nc, gt = false;
+#pragma unroll
+                for (int f = 0; f < NFIELD; ++f) {
+                    ge = ge && v[f][a] >= v[f][b];
+                    gt = gt || v[f][a] > v[f][b];
+                }
+                dominated = dominated || (ge && (gt || a < b));  // of identical cards the first stays
+                if (((hm >> a) & 1u) && (v[F_FREE][a] > v[F_FREE][b] || (v[F_FREE][a] == v[F_FREE][b] && a < b))) rank++;
+            }
+            if (!dominated) keep |= 1u << b;
+            if ((hm >> b) & 1u) {
+#pragma unroll
+                for (int k = 0; k < G; ++k)
+                    if (rank == (u32)k) tk[k] = (u32)v[F_FREE][b];
+            }
+        }
+        s.meta[n] = (meta & 0x00FFFFFFu) | (keep << 24);
+        uint4 *dst = reinterpret_cast<uint4 *>(s.tk32 + (size_t)n * G);
+        dst[0] = make_uint4(tk[0], tk[1], tk[2], tk[3]);
+        dst[1] = make_uint4(tk[4], tk[5], tk[6], tk[7]);
+    }
     const u32 key = (meta & META_HAS_SCV) ? min((u32)s.f[F_CLOCK][(size_t)n * G], 0xFFFFFFFDu) : 0xFFFFFFFEu;
     if (s.order_key[n] != key) {
         s.order_key[n] = key;

@@ -221,29 +221,14 @@ __global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupD
     const u32 nn = live ? s.order[slot] : 0;  // nodes with the same clock sit in the same warps
     const u32 meta = live ? s.meta[nn] : 0u;
     const bool has = (meta & META_HAS_SCV) != 0;
-    const u32 nc = meta_ncards(meta), hm = meta_healthy(meta);
+    const u32 hm = meta_healthy(meta), keep = meta_keep(meta);
     const u32 cardnum = s.cardnum32[nn];
-    u32 fr[G], ck[G];
-    load8(s.n32[F_FREE] + (size_t)nn * G, fr);
-    load8(s.n32[F_CLOCK] + (size_t)nn * G, ck);
+    const u32 n_healthy = __popc(hm);
     // Tk[k-1] = k-th largest FreeMemory among healthy cards: the node admits memory values m <= Tk[num-1]
     // when scv/memory is present (filter.go:18-33)
-    u32 Tk[G];
-#pragma unroll
-    for (int k = 0; k < G; ++k) Tk[k] = 0;
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-        if ((hm >> g) & 1u) {
-            u32 rank = 0;
-#pragma unroll
-            for (int h = 0; h < G; ++h)
-                if (((hm >> h) & 1u) && (fr[h] > fr[g] || (fr[h] == fr[g] && h < g))) rank++;
-#pragma unroll
-            for (int k = 0; k < G; ++k)
-                if (rank == (u32)k) Tk[k] = fr[g];
-        }
-    }
-    const u32 n_healthy = __popc(hm);
+    u32 ck[G], Tk[G];
+    load8(s.n32[F_CLOCK] + (size_t)nn * G, ck);
+    load8(s.tk32 + (size_t)nn * G, Tk);
     // blockIdx.y takes every gridDim.y-th tile of groups
     for (u32 g0 = blockIdx.y * MAXG_TILE; g0 < n_groups; g0 += MAXG_TILE * gridDim.y) {
         __syncthreads();
@@ -251,51 +236,82 @@ __global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupD
         __syncthreads();
         const u32 gn = min(MAXG_TILE, n_groups - g0);
         if (!has) continue;
-        for (u32 gi = 0; gi < gn; ++gi) {
+        // which groups of the tile this node is feasible for, and the memory bound T it admits in each
+        u32 T[MAXG_TILE], pass = 0;
+#pragma unroll
+        for (int gi = 0; gi < MAXG_TILE; ++gi) {
+            T[gi] = 0xFFFFFFFFu;
+            if (gi >= (int)gn) continue;
             const GroupDesc gd = sg[gi];
-            if (gd.num > cardnum) continue;  // filter.go:13,15
-            if (gd.flags & YODA_POD_HAS_CLOCK) {  // filter.go:35-50
+            bool ok = gd.num <= cardnum && gd.seg_end > gd.seg_start;  // filter.go:13,15
+            if (gd.flags & YODA_POD_HAS_CLOCK) {                       // filter.go:35-50
                 u32 cnt = 0;
 #pragma unroll
                 for (int g = 0; g < G; ++g) cnt += ((hm >> g) & 1u) & (u32)(ck[g] == gd.c);
-                if (cnt < gd.num) continue;
+                ok = ok && cnt >= gd.num;
             }
-            u32 T = 0xFFFFFFFFu;
-            if ((gd.flags & YODA_POD_HAS_MEMORY) && gd.num >= 1) {
-                if (n_healthy < gd.num) continue;
-                T = 0;
+            if ((gd.flags & YODA_POD_HAS_MEMORY) && gd.num >= 1) {     // filter.go:18-33
+                ok = ok && n_healthy >= gd.num;
+                u32 t = 0;
 #pragma unroll
                 for (int k = 0; k < G; ++k)
-                    if (gd.num == (u32)(k + 1)) T = Tk[k];
+                    if (gd.num == (u32)(k + 1)) t = Tk[k];
+                T[gi] = t;
             }
-            const u32 *ms = m_sorted + gd.seg_start;
-            const u32 len = gd.seg_end - gd.seg_start;
-            if (!len) continue;
-            // j[g] = number of pods of the group with memory <= e[g], for the eight cards at once: a branch-free
-            // upper bound with the same trip count for every card, so eight independent loads are in flight per step
-            u32 e[G], j[G];
+            pass |= ok ? (1u << gi) : 0u;
+        }
+        if (!pass) continue;
+        // Only cards that no other card of the node dominates can hold a maximum (a dominating card is admitted
+        // by every pod that admits the dominated one); homogeneous nodes keep a single card.
+        for (u32 km = keep; km; km &= km - 1) {
+            const int g = __ffs(km) - 1;
+            const size_t o = (size_t)nn * G + g;
+            const u32 frg = s.n32[F_FREE][o], ckg = s.n32[F_CLOCK][o];
+            // j[gi] = number of pods of group gi with memory <= min(frg, T[gi]): branch-free upper bounds, the
+            // groups of the tile side by side so that their loads are in flight together
+            u32 j[MAXG_TILE], rem[MAXG_TILE], more = 0;
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                e[g] = min(fr[g], T);
-                j[g] = 0;
+            for (int gi = 0; gi < MAXG_TILE; ++gi) {
+                j[gi] = 0;
+                const bool act = ((pass >> gi) & 1u) && ckg >= sg[gi].c;  // collection.go:46 (clock >= c; c == 0 without the label)
+                rem[gi] = act ? sg[gi].seg_end - sg[gi].seg_start : 0u;
+                more |= rem[gi] > 1 ? 1u : 0u;
             }
-            for (u32 rem = len; rem > 1;) {
-                const u32 half = rem >> 1;
+            while (more) {
+                more = 0;
 #pragma unroll
-                for (int g = 0; g < G; ++g) j[g] += (ms[j[g] + half - 1] <= e[g]) ? half : 0u;
-                rem -= half;
+                for (int gi = 0; gi < MAXG_TILE; ++gi) {
+                    if (rem[gi] > 1) {
+                        const u32 half = rem[gi] >> 1;
+                        j[gi] += (m_sorted[sg[gi].seg_start + j[gi] + half - 1] <= min(frg, T[gi])) ? half : 0u;
+                        rem[gi] -= half;
+                        more |= rem[gi] > 1 ? 1u : 0u;
+                    }
+                }
             }
+            // collection.go:59-78; order of the step planes = collection.MaxValue (bw, clock, core, free, power, total)
+            const u32 v[6] = {s.n32[F_BW][o], ckg, s.n32[F_CORE][o], frg, s.n32[F_POWER][o], s.n32[F_TOTAL][o]};
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                j[g] += (ms[j[g]] <= e[g]) ? 1u : 0u;
-                if (g >= (int)nc || ck[g] < gd.c || j[g] == 0) continue;  // collection.go:46 (clock >= c; c == 0 without the label)
-                const u32 pos = gd.seg_start + j[g] - 1;
-                const size_t o = (size_t)nn * G + g;
-                // collection.go:59-78; order of the step planes = collection.MaxValue (bw, clock, core, free, power, total)
-                const u32 v[6] = {s.n32[F_BW][o], ck[g], s.n32[F_CORE][o], fr[g], s.n32[F_POWER][o], s.n32[F_TOTAL][o]};
+            for (int gi = 0; gi < MAXG_TILE; ++gi) {
+                if (!rem[gi]) continue;
+                const u32 cnt = j[gi] + ((m_sorted[sg[gi].seg_start + j[gi]] <= min(frg, T[gi])) ? 1u : 0u);
+                if (!cnt) continue;
+                const u32 pos = sg[gi].seg_start + cnt - 1;
+                // Short segments (small batches above all) send every lane to the same position: one atomic per warp
+                // then, not one per lane.  Any set of lanes that happens to be here together may team up.
+                const u32 team = __activemask();
+                const u32 lead = __ffs(team) - 1;
+                const bool same = __all_sync(team, pos == __shfl_sync(team, pos, lead));
 #pragma unroll
-                for (int f = 0; f < 6; ++f)
-                    if (v[f] > step[(size_t)f * P + pos]) atomicMax(&step[(size_t)f * P + pos], v[f]);
+                for (int f = 0; f < 6; ++f) {
+                    u32 *dst = &step[(size_t)f * P + pos];
+                    if (same) {
+                        const u32 m = __reduce_max_sync(team, v[f]);
+                        if ((threadIdx.x & 31) == lead && m > __ldcg(dst)) atomicMax(dst, m);
+                    } else if (v[f] > __ldcg(dst)) {  // L2: sees the other SMs' maxima
+                        atomicMax(dst, v[f]);
+                    }
+                }
             }
         }
     }

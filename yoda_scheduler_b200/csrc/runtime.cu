@@ -243,6 +243,7 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
     if (!rc) rc = dev_alloc(&s.cardnum32, cap);
     if (!rc) rc = dev_alloc(&s.stat32, cap);
     if (!rc) rc = dev_alloc(&c->d_wide_flag, 2);
+    if (!rc) rc = dev_alloc(&s.tk32, (size_t)cap * G);
     if (!rc) rc = dev_alloc(&s.order, cap);
     if (!rc) rc = dev_alloc(&s.order_key, cap);
     if (!rc) rc = dev_alloc(&c->ord_keys_out, cap);
@@ -284,7 +285,7 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     dev_free(s.card_number); dev_free(s.free_sum); dev_free(s.total_sum); dev_free(s.alloc_sum);
     dev_free(s.stat); dev_free(s.meta);
     for (int f = 0; f < NFIELD; ++f) dev_free(s.n32[f]);
-    dev_free(s.cardnum32); dev_free(s.stat32); dev_free(s.order); dev_free(s.order_key);
+    dev_free(s.cardnum32); dev_free(s.stat32); dev_free(s.tk32); dev_free(s.order); dev_free(s.order_key);
     dev_free(c->ord_keys_out); dev_free(c->ord_iota);
     if (c->ord_tmp) cudaFree(c->ord_tmp);
     dev_free(c->d_wide_flag); dev_free(c->d_lohi); dev_free(c->d_list); dev_free(c->d_upd);
