@@ -690,10 +690,10 @@ struct ScoreSmem {
 template <int NPL, bool DECIDE>
 __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u32 tile, u32 chunk, const DevSnap &s,
                                            const PodS *__restrict__ pods, u32 p_begin, u32 p_end, const u32 *__restrict__ tables,
-                                           u64 *hilo, u64 *count, u64 *dkey) {
+                                           u64 *hilo, u64 *count, u64 *dkey, u32 chunk_pods) {
     const u32 lane = tid & 31, warp = tid >> 5;
-    const u32 c0 = p_begin + chunk * HOT_CHUNK;
-    const u32 cn = min(HOT_CHUNK, p_end - c0);
+    const u32 c0 = p_begin + chunk * chunk_pods;
+    const u32 cn = min(chunk_pods, p_end - c0);
     for (u32 i = tid; i < cn * 2; i += HOT_THREADS) sm.sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
     const u32 base = (tile * HOT_WARPS + warp) * (NPL * 32);
     u32 node[NPL], cardnum[NPL], stat[NPL];
@@ -844,10 +844,10 @@ template <int NPL, bool WRITE>
 __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 tile, u32 chunk, const DevSnap &s,
                                          const PodS *__restrict__ pods, const u64 *__restrict__ hilo, u32 p_begin, u32 p_end,
                                          const u32 *__restrict__ tables, u64 *count, u64 *ckey, i64 *raw_out, u8 *norm_out, u32 *bits_out,
-                                         u64 stride) {
+                                         u64 stride, u32 chunk_pods) {
     const u32 lane = tid & 31, warp = tid >> 5;
-    const u32 c0 = p_begin + chunk * HOT_CHUNK;
-    const u32 cn = min(HOT_CHUNK, p_end - c0);
+    const u32 c0 = p_begin + chunk * chunk_pods;
+    const u32 cn = min(chunk_pods, p_end - c0);
     for (u32 i = tid; i < cn * 2; i += HOT_THREADS) sm.sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
     for (u32 i = tid; i < cn; i += HOT_THREADS) sm.sn[i] = norm_consts(hilo, pods[c0 + i].orig);
     const u32 base = (tile * HOT_WARPS + warp) * (NPL * 32);
@@ -962,16 +962,17 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
 
 template <int NPL, bool DECIDE>
 __global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
-                                                            const u32 *__restrict__ tables, u64 *hilo, u64 *count, u64 *dkey) {
+                                                            const u32 *__restrict__ tables, u64 *hilo, u64 *count, u64 *dkey,
+                                                            u32 chunk_pods) {  // pods per CTA: a multiple of SCORE_BLK, <= HOT_CHUNK
     __shared__ ScoreSmem sm;
-    score_body<NPL, DECIDE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo, count, dkey);
+    score_body<NPL, DECIDE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo, count, dkey, chunk_pods);
 }
 
 template <int NPL, bool WRITE>
 __global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_out(DevSnap s, const PodS *__restrict__ pods, const u64 *__restrict__ hilo,
                                                              u32 p_begin, u32 p_end, const u32 *__restrict__ tables, u64 *count, u64 *ckey,
-                                                             i64 *raw_out, u8 *norm_out, u32 *bits_out, u64 stride) {
+                                                             i64 *raw_out, u8 *norm_out, u32 *bits_out, u64 stride, u32 chunk_pods) {
     __shared__ OutSmem sm;
     out_body<NPL, WRITE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, hilo, p_begin, p_end, tables, count, ckey, raw_out, norm_out,
-                         bits_out, stride);
+                         bits_out, stride, chunk_pods);
 }

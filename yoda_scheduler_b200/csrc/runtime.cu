@@ -89,6 +89,8 @@ static int nccl_load() {
 // ------------------------------------------------------------------------------------------
 enum { EV_START = 0, EV_PREP, EV_MAX, EV_SCORE, EV_WRITE, EV_H2D0, EV_H2D1, EV_D2H0, EV_D2H1, EV_COUNT };
 
+#define SCORE_NPL 4  // nodes per lane in the score pass (its per-node state is 7 registers)
+
 struct yoda_ctx {
     std::mutex mu;
     yoda_config cfg{};
@@ -156,6 +158,7 @@ struct yoda_ctx {
     u64 *sq_alloc = nullptr;
     u32 *sq_stat = nullptr, *sq_pos = nullptr, *sq_order = nullptr, *sq_status = nullptr;
     u32 sq_pods_cap = 0;
+    u32 score_slots = 0, out_slots = 0;  // CTAs of the hot kernels resident on the device at once
     int n_sms = 0;  // DECIDE on one GPU: the score pass also yields counts and the node choice
 };
 
@@ -224,6 +227,14 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
         return bail(fail(YODA_E_CUDA, "cudaStreamCreate failed"));
     c->stream = c->own_stream;
     if (cudaDeviceGetAttribute(&c->n_sms, cudaDevAttrMultiProcessorCount, cfg->device) != cudaSuccess || c->n_sms <= 0) c->n_sms = 148;
+    {
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fast_score<SCORE_NPL, false>, HOT_THREADS, 0) != cudaSuccess || per_sm <= 0) per_sm = 2;
+        c->score_slots = (u32)per_sm * (u32)c->n_sms;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fast_out<4, true>, HOT_THREADS, 0) != cudaSuccess || per_sm <= 0) per_sm = 2;
+        c->out_slots = (u32)per_sm * (u32)c->n_sms;
+        cudaGetLastError();
+    }
     for (int i = 0; i < EV_COUNT; ++i)
         if (cudaEventCreate(&c->ev[i]) != cudaSuccess) return bail(fail(YODA_E_CUDA, "cudaEventCreate failed"));
     const u32 cap = round_up(cfg->max_nodes, 128);
@@ -681,34 +692,44 @@ static int fast_phase0(yoda_ctx *c) {
     return YODA_OK;
 }
 
-static dim3 hot_grid(const yoda_ctx *c, u32 n_pods) {
-    constexpr int NPL = 4;
-    return dim3((c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32), (n_pods + HOT_CHUNK - 1) / HOT_CHUNK);
+// Pods per CTA of the two hot kernels.  HOT_CHUNK for big batches; for small and medium ones the last wave of CTAs
+// would be mostly empty, so the chunk shrinks until the CTAs fill whole waves (slots = CTAs resident at once).
+static u32 hot_chunk(u32 n_pods, u32 tiles, u32 slots) {
+    const u32 chunks = (n_pods + HOT_CHUNK - 1) / HOT_CHUNK;
+    const u32 waves = (tiles * chunks + slots - 1) / slots;
+    const u32 want = std::max(chunks, waves * slots / std::max(tiles, 1u));  // chunks that still fit those waves
+    u32 chunk = (n_pods + want - 1) / want;
+    chunk = std::min<u32>(HOT_CHUNK, std::max<u32>(16u, (chunk + SCORE_BLK - 1) / SCORE_BLK * SCORE_BLK));
+    return chunk;
 }
 
-#define SCORE_NPL 4  // nodes per lane in the score pass (its per-node state is 7 registers)
 static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
-    const dim3 grid((c->snap.n_nodes + HOT_WARPS * SCORE_NPL * 32 - 1) / (HOT_WARPS * SCORE_NPL * 32), (p_end - p_begin + HOT_CHUNK - 1) / HOT_CHUNK);
+    const u32 tiles = (c->snap.n_nodes + HOT_WARPS * SCORE_NPL * 32 - 1) / (HOT_WARPS * SCORE_NPL * 32);
+    const u32 chunk = hot_chunk(p_end - p_begin, tiles, c->score_slots);
+    const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
     if (c->fw_decide_merged)
         k_fast_score<SCORE_NPL, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
-                                                                           c->d_count, c->d_ckey);
+                                                                           c->d_count, c->d_ckey, chunk);
     else
         k_fast_score<SCORE_NPL, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
-                                                                            c->d_count, c->d_ckey);
+                                                                            c->d_count, c->d_ckey, chunk);
     LAUNCHED(c);
     return YODA_OK;
 }
 
 static int fast_out_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
-    const dim3 grid = hot_grid(c, p_end - p_begin);
+    constexpr int NPL = 4;
+    const u32 tiles = (c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32);
+    const u32 chunk = hot_chunk(p_end - p_begin, tiles, c->out_slots);
+    const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
     if (c->ph_flags & YODA_EVAL_FULL)
         k_fast_out<4, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
-                                                                 c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride);
+                                                                 c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride, chunk);
     else
         k_fast_out<4, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
-                                                                  c->d_ckey, nullptr, nullptr, nullptr, c->stride);
+                                                                  c->d_ckey, nullptr, nullptr, nullptr, c->stride, chunk);
     LAUNCHED(c);
     return YODA_OK;
 }
