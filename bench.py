@@ -33,9 +33,12 @@ W_BYTES = 9.125      # int64 raw + uint8 normalized + 1 feasible bit per (pod, n
 R_NODE, R_POD, R_OUT = 208, 32, 72
 
 
-def algorithmic_bytes(P, N):
+W_BYTES_RAW32 = 5.125  # YODA_EVAL_RAW32: the same scores as uint32 (SURVEY.md 8(d) allows restating W this way)
+
+
+def algorithmic_bytes(P, N, w=W_BYTES):
     """N*R_node + P*R_pod + P*R_out + P*N*W."""
-    return N * R_NODE + P * R_POD + P * R_OUT + P * N * W_BYTES
+    return N * R_NODE + P * R_POD + P * R_OUT + P * N * w
 
 
 def profiled_traffic(config, mode, path):
@@ -169,6 +172,7 @@ def main():
     ap.add_argument("--shard", default="nodes", choices=["nodes", "pods"],
                     help="N>1: nodes = each GPU owns a slice of the cluster, pods replicated, three small exchanges (BASELINE config 4); "
                          "pods = snapshot replicated, each GPU takes its own pods, no exchange at all")
+    ap.add_argument("--raw32", action="store_true", help="FULL mode with the Score matrix stored as uint32 (YODA_EVAL_RAW32, W = 5.125 B)")
     ap.add_argument("--round-values", action="store_true", help="pod variant with round scv/memory values (few requirement classes)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
@@ -197,6 +201,9 @@ def main():
     snap = synth.make_snapshot(n_nodes, node_offset=node_base)
     reqs_np = synth.make_requests(n_pods, pod_seed + (rank if pod_sharded else 0), args.round_values)
     flags = (api.EVAL_FULL if args.mode == "full" else api.EVAL_DECIDE) | (api.EVAL_FORCE_DIRECT if args.force_direct else 0)
+    if args.raw32 and args.mode == "full":
+        flags |= api.EVAL_RAW32
+    w_bytes = W_BYTES_RAW32 if (flags & api.EVAL_RAW32) else W_BYTES
 
     ctx = api.Context(n_nodes, device=local_rank, node_base=node_base, shard_rank=0 if pod_sharded else rank, shard_count=1 if pod_sharded else world)
     if world > 1 and not pod_sharded:
@@ -320,9 +327,9 @@ def main():
         # dominant kernel = the output pass (Filter+Score+NormalizeScore -> matrices); per launch it
         # moves the whole batch's matrices for this GPU's shard
         kern_ms = phase["write"] / steps
-        kern_bytes = n_pods * n_nodes * (W_BYTES if full else 0.0) + n_nodes * R_NODE + n_pods * (R_POD + R_OUT)
+        kern_bytes = n_pods * n_nodes * (w_bytes if full else 0.0) + n_nodes * R_NODE + n_pods * (R_POD + R_OUT)
         achieved = kern_bytes / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else 0.0
-        step_bytes = algorithmic_bytes(n_pods, n_nodes) if full else n_nodes * R_NODE + n_pods * (R_POD + R_OUT)
+        step_bytes = algorithmic_bytes(n_pods, n_nodes, w_bytes) if full else n_nodes * R_NODE + n_pods * (R_POD + R_OUT)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if (args.config == "c4" and not pod_sharded) else "weak", "vs_baseline": None, "dtype": "u64" if t_last.path == 0 else "u32",
@@ -330,14 +337,15 @@ def main():
             "config": {"workload": (f"{args.config}: {n_nodes} nodes x 8 cards replicated on every GPU, {n_pods} pods per GPU ({total_pods} total, pod-sharded, no exchange), mode={args.mode}"
                                     if pod_sharded else
                                     f"{args.config}: {n_nodes} nodes x 8 cards per GPU ({total_nodes} total, node-sharded), {n_pods} pods, mode={args.mode}")
-                                   + (", round scv/memory values" if args.round_values else ""),
+                                   + (", round scv/memory values" if args.round_values else "")
+                                   + (", Score matrix as uint32 (W = 5.125 B per evaluation)" if flags & api.EVAL_RAW32 else ""),
                        "l2": "every step writes the result matrices (>> 126 MB L2), which sweeps L2 between iterations; the snapshot is L2-resident by design",
                        "path": "narrow-fast" if t_last.path == 1 else "direct-u64", "classes": t_last.n_classes, "groups": t_last.n_groups},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(reqs_np.nbytes), "d2h_bytes_per_step": int(n_pods * api.POD_RES.itemsize)},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "output pass (write_ms)", "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": profiled_traffic(args.config, args.mode, t_last.path), "algorithmic_bytes": kern_bytes,
+                         "frac": achieved / peak, "traffic": None if flags & api.EVAL_RAW32 else profiled_traffic(args.config, args.mode, t_last.path), "algorithmic_bytes": kern_bytes,
                          "step_achieved": step_bytes / (phase["total"] / steps * 1e-3) / 1e9 if phase["total"] > 0 else 0.0,
                          "step_frac": step_bytes / (phase["total"] / steps * 1e-3) / 1e9 / peak if phase["total"] > 0 else 0.0,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
@@ -362,6 +370,28 @@ def main():
             dms = d0.elapsed_time(d1) / 10
             line["decide_mode"] = {"ms_per_step": dms, "value": evals / (dms * 1e-3), "unit": UNIT,
                                    "note": "YODA_EVAL_DECIDE: maxima, lowest/highest, feasible count and chosen node per pod; no matrices"}
+        if world == 1 and args.mode == "full" and not args.no_latency and not (flags & api.EVAL_RAW32) and t_last.path == 1:
+            # the same batch with the Score matrix stored as uint32 (YODA_EVAL_RAW32): W = 5.125 B per evaluation
+            rflags = flags | api.EVAL_RAW32
+            for _ in range(3):
+                ctx.eval_device(d_reqs.data_ptr(), n_pods, rflags)
+            ctx.sync()
+            r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            wsum = 0.0
+            with torch.cuda.stream(stream):
+                r0.record(stream)
+                for _ in range(10):
+                    ctx.eval_device(d_reqs.data_ptr(), n_pods, rflags)
+                    wsum += ctx.timing().write_ms
+                r1.record(stream)
+            torch.cuda.synchronize()
+            rms = r0.elapsed_time(r1) / 10
+            rbytes = n_pods * n_nodes * W_BYTES_RAW32 + n_nodes * R_NODE + n_pods * (R_POD + R_OUT)
+            line["raw32_mode"] = {"ms_per_step": rms, "value": evals / (rms * 1e-3), "unit": UNIT, "write_ms": wsum / 10,
+                                  "output_pass_GBps": rbytes / (wsum / 10 * 1e-3) / 1e9, "output_pass_frac_of_peak": rbytes / (wsum / 10 * 1e-3) / 1e9 / peak,
+                                  "note": "YODA_EVAL_FULL | YODA_EVAL_RAW32: identical scores stored as uint32, W = 5.125 B per evaluation"}
+            ctx.eval_device(d_reqs.data_ptr(), n_pods, flags)   # leave the int64 result behind for what follows
+            ctx.sync()
         if world == 1 and not args.no_latency:
             # p50/p99 batch latency at this snapshot size, host buffers in -> per-pod results out
             lat = {}

@@ -90,6 +90,12 @@ typedef struct {
 #define YODA_EVAL_DECIDE 0u       /* per-pod results only */
 #define YODA_EVAL_FULL 1u         /* also materialise feasible bits, raw and normalized scores in HBM */
 #define YODA_EVAL_FORCE_DIRECT 2u /* use the exact-u64 direct kernels even when the narrow path applies */
+/* With YODA_EVAL_FULL: store the Score matrix as uint32 instead of int64.  Every Score of a narrow snapshot is
+ * below 2^32 (it is what the fast path computes in), so this only drops the 32 zero bits of each int64 and with
+ * them almost half of the bytes the output pass writes (9.125 -> 5.125 per pod x node).  A request, not a
+ * guarantee: a batch that has to take the exact-u64 kernels still gets int64 rows; yoda_result_raw_bytes tells
+ * which, and yoda_fetch_row(YODA_ROW_RAW) delivers int64 either way. */
+#define YODA_EVAL_RAW32 4u
 
 /* rows of the device-resident result matrices (YODA_EVAL_FULL) */
 #define YODA_ROW_FEASIBLE_BITS 0 /* uint32 words, bit (n & 31) of word n >> 5 = node n passed Filter */
@@ -145,6 +151,8 @@ int yoda_sync(yoda_ctx *ctx);
 int yoda_last_timing(yoda_ctx *ctx, yoda_timing *t);
 /* device pointers of the last YODA_EVAL_FULL matrices (for zero-copy consumers); row strides in elements */
 int yoda_result_matrices(yoda_ctx *ctx, void **d_bits, void **d_raw, void **d_norm, uint64_t *stride_nodes);
+/* element size of the raw matrix of the last YODA_EVAL_FULL result: 8 (int64), or 4 (uint32, YODA_EVAL_RAW32 honoured) */
+int yoda_result_raw_bytes(yoda_ctx *ctx, uint32_t *bytes);
 
 /* Yoda.NormalizeScore on an arbitrary score list, in place, on the device (scheduler.go:132-157):
  * used when the framework's list is not Yoda's own feasible set (other plugins filtered too). */

@@ -425,3 +425,56 @@ def test_maxima_scan_across_tiles():
     res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_DECIDE, fetch=False)
     assert t.path == 1 and t.n_groups > 50
     assert_matches_oracle(snap, labels, res, None)
+
+
+def test_raw32_matrix_equals_int64_matrix():
+    """YODA_EVAL_RAW32: the Score matrix stored as uint32.  Same per-pod results, same rows through
+    yoda_fetch_row, and read straight from the device the uint32 matrix is the int64 one narrowed."""
+    import torch
+    from yoda_scheduler_b200 import shard
+    N, P = 3000, 700
+    snap = synth.make_snapshot(N)
+    reqs = synth.make_requests(P, 5)
+    with api.Context(N) as ctx:
+        ctx.load_snapshot(snap)
+        want = ctx.eval(reqs, api.EVAL_FULL)
+        assert ctx.result_raw_bytes() == 8
+        want_m = ctx.fetch_all(P)
+        got = ctx.eval(reqs, api.EVAL_FULL | api.EVAL_RAW32)
+        assert ctx.result_raw_bytes() == 4 and ctx.timing().path == 1
+        got_m = ctx.fetch_all(P)
+        assert np.array_equal(got, want)
+        for k in want_m:
+            assert np.array_equal(got_m[k], want_m[k]), k
+        import ctypes as C
+        d_raw, stride = C.c_void_p(), C.c_uint64()
+        api.check(ctx.L.yoda_result_matrices(ctx.h, None, C.byref(d_raw), None, C.byref(stride)))
+        t = shard.device_tensor(d_raw.value, P * stride.value // 2, torch.device("cuda", 0))   # uint64 words = 2 scores each
+        dev = t.cpu().numpy().view(np.uint32).reshape(P, stride.value)[:, :N]
+        assert np.array_equal(dev.astype(np.int64), want_m["raw"])
+        # a forced-direct batch cannot honour the request: int64 rows, same values
+        got = ctx.eval(reqs[:50], api.EVAL_FULL | api.EVAL_RAW32 | api.EVAL_FORCE_DIRECT)
+        assert ctx.result_raw_bytes() == 8
+        assert np.array_equal(got, want[:50])
+        assert np.array_equal(ctx.fetch_all(50)["raw"], want_m["raw"][:50])
+    assert_matches_oracle(snap, synth.make_pod_labels(P, 5), want, want_m)
+
+
+def test_raw32_request_survives_a_fallback():
+    """The class-table overflow case with YODA_EVAL_RAW32: the exact kernels take over, the rows are int64."""
+    nodes = [{"name": f"n{i}", "has_scv": True, "card_number": 2, "free_sum": 5000, "total_sum": 16000, "pods": [],
+              "cards": [{"health": "Healthy", "free": 4000 + i, "total": 8000, "clock": 30_000_000 + i, "core": 100, "bandwidth": 1 + (i % 3), "power": 50},
+                        {"health": "Healthy", "free": 1000, "total": 8000, "clock": 1000, "core": 100, "bandwidth": 2, "power": 50}]}
+             for i in range(70)]
+    snap = Snapshot.from_nodes(nodes)
+    for n_pods in (3, 40):
+        labels = [{"scv/memory": str(500 + 37 * k)} for k in range(n_pods)]
+        with api.Context(70) as ctx:
+            ctx.load_snapshot(snap)
+            res = ctx.eval(pods_to_requests(labels), api.EVAL_FULL | api.EVAL_RAW32)
+            assert ctx.timing().path == 0 and ctx.result_raw_bytes() == 8
+            assert_matches_oracle(snap, labels, res, ctx.fetch_all(n_pods))
+    with api.Context(70) as ctx:
+        ctx.load_snapshot(snap)
+        with pytest.raises(api.YodaError):
+            ctx.eval(pods_to_requests(labels), 64)          # unknown flag bits are rejected

@@ -10,7 +10,7 @@ from . import _lib
 from ._lib import Config, Timing, Xchg, YodaError, check  # noqa: F401
 from .snapshot import NODE_REC, POD_REQ, POD_RES, Snapshot
 
-EVAL_DECIDE, EVAL_FULL, EVAL_FORCE_DIRECT = 0, 1, 2
+EVAL_DECIDE, EVAL_FULL, EVAL_FORCE_DIRECT, EVAL_RAW32 = 0, 1, 2, 4
 ROW_FEASIBLE_BITS, ROW_RAW, ROW_NORM = 0, 1, 2
 
 
@@ -113,6 +113,12 @@ class Context:
         out = np.zeros(n, np.int64 if kind == ROW_RAW else np.uint8)
         check(self.L.yoda_fetch_row(self.h, pod, kind, out.ctypes.data, out.nbytes))
         return out
+
+    def result_raw_bytes(self) -> int:
+        """4 when the last FULL result holds uint32 scores (EVAL_RAW32 honoured), else 8."""
+        b = C.c_uint32()
+        check(self.L.yoda_result_raw_bytes(self.h, C.byref(b)))
+        return b.value
 
     def fetch_all(self, n_pods: int) -> dict:
         n = self.node_count()

@@ -840,7 +840,7 @@ __device__ __forceinline__ uint4 norm_consts(const u64 *__restrict__ hilo, u32 o
 // output pass: feasible bits, Score (int64), NormalizeScore (uint8), feasible count, node choice.
 // Rows are padded to the CTA tile (stride % (HOT_WARPS*NPL*32) == 0), so no lane is out of range:
 // lanes past the last node hold no SCV, score 0 and write into the padding.
-template <int NPL, bool WRITE>
+template <int NPL, bool WRITE, bool RAW32>
 __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 tile, u32 chunk, const DevSnap &s,
                                          const PodS *__restrict__ pods, const u64 *__restrict__ hilo, u32 p_begin, u32 p_end,
                                          const u32 *__restrict__ tables, u64 *count, u64 *ckey, i64 *raw_out, u8 *norm_out, u32 *bits_out,
@@ -935,8 +935,14 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
             const size_t row = (size_t)pod.orig * stride;
             // streaming stores (written once, never re-read by this pass); every instruction covers whole sectors:
             // 2 x 512 B of scores and 2 x 64 B of normalized scores per warp
-            __stcs(reinterpret_cast<ulonglong2 *>(rawp + row), make_ulonglong2(raw64[0], raw64[1]));
-            __stcs(reinterpret_cast<ulonglong2 *>(rawp + row + 64), make_ulonglong2(raw64[2], raw64[3]));
+            if (RAW32) {  // YODA_EVAL_RAW32: the same values without their zero high words, 2 x 256 B per warp
+                u32 *rawp32 = reinterpret_cast<u32 *>(raw_out) + base + 2 * lane;
+                __stcs(reinterpret_cast<uint2 *>(rawp32 + row), make_uint2((u32)raw64[0], (u32)raw64[1]));
+                __stcs(reinterpret_cast<uint2 *>(rawp32 + row + 64), make_uint2((u32)raw64[2], (u32)raw64[3]));
+            } else {
+                __stcs(reinterpret_cast<ulonglong2 *>(rawp + row), make_ulonglong2(raw64[0], raw64[1]));
+                __stcs(reinterpret_cast<ulonglong2 *>(rawp + row + 64), make_ulonglong2(raw64[2], raw64[3]));
+            }
             __stcs(reinterpret_cast<unsigned short *>(normp + row), (unsigned short)(qn[0] | (qn[1] << 8)));
             __stcs(reinterpret_cast<unsigned short *>(normp + row + 64), (unsigned short)(qn[2] | (qn[3] << 8)));
             if (lane == 0) __stcs(reinterpret_cast<uint4 *>(bitsp + (size_t)pod.orig * (stride >> 5)), make_uint4(fitw[0], fitw[1], fitw[2], fitw[3]));
@@ -968,11 +974,11 @@ __global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const Pod
     score_body<NPL, DECIDE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo, count, dkey, chunk_pods);
 }
 
-template <int NPL, bool WRITE>
+template <int NPL, bool WRITE, bool RAW32>
 __global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_out(DevSnap s, const PodS *__restrict__ pods, const u64 *__restrict__ hilo,
                                                              u32 p_begin, u32 p_end, const u32 *__restrict__ tables, u64 *count, u64 *ckey,
                                                              i64 *raw_out, u8 *norm_out, u32 *bits_out, u64 stride, u32 chunk_pods) {
     __shared__ OutSmem sm;
-    out_body<NPL, WRITE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, hilo, p_begin, p_end, tables, count, ckey, raw_out, norm_out,
+    out_body<NPL, WRITE, RAW32>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, hilo, p_begin, p_end, tables, count, ckey, raw_out, norm_out,
                          bits_out, stride, chunk_pods);
 }

@@ -116,7 +116,8 @@ struct yoda_ctx {
     u64 *d_max6 = nullptr, *d_count = nullptr, *d_hilo = nullptr, *d_ckey = nullptr;
     yoda_pod_result *d_res = nullptr, *h_res = nullptr;
     // result matrices
-    size_t raw_cap = 0, bits_cap = 0;
+    size_t raw_cap = 0, norm_cap = 0, bits_cap = 0;  // raw_cap in bytes, the others in elements
+    bool res_raw32 = false;  // the raw matrix of the current result holds uint32 (YODA_EVAL_RAW32 honoured)
     i64 *d_raw = nullptr;
     u8 *d_norm = nullptr;
     u32 *d_bits = nullptr;
@@ -231,7 +232,7 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
         int per_sm = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fast_score<SCORE_NPL, false>, HOT_THREADS, 0) != cudaSuccess || per_sm <= 0) per_sm = 2;
         c->score_slots = (u32)per_sm * (u32)c->n_sms;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fast_out<4, true>, HOT_THREADS, 0) != cudaSuccess || per_sm <= 0) per_sm = 2;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fast_out<4, true, false>, HOT_THREADS, 0) != cudaSuccess || per_sm <= 0) per_sm = 2;
         c->out_slots = (u32)per_sm * (u32)c->n_sms;
         cudaGetLastError();
     }
@@ -496,16 +497,25 @@ static int ensure_pods(yoda_ctx *c, u32 P) {
     return YODA_OK;
 }
 
-static int ensure_matrices(yoda_ctx *c, u32 P, u64 stride) {
+static int ensure_raw(yoda_ctx *c, size_t bytes) {
+    if (bytes <= c->raw_cap) return YODA_OK;
+    CU(cudaStreamSynchronize(c->stream));
+    dev_free(c->d_raw);
+    c->raw_cap = 0;
+    TRY(dev_alloc((u8 **)&c->d_raw, bytes));
+    c->raw_cap = bytes;
+    return YODA_OK;
+}
+
+static int ensure_matrices(yoda_ctx *c, u32 P, u64 stride, u32 raw_elem_bytes) {
     const size_t need = (size_t)P * stride, need_bits = (size_t)P * (stride / 32);
-    if (need > c->raw_cap) {
+    TRY(ensure_raw(c, need * raw_elem_bytes));
+    if (need > c->norm_cap) {
         CU(cudaStreamSynchronize(c->stream));
-        dev_free(c->d_raw);
         dev_free(c->d_norm);
-        c->raw_cap = 0;
-        TRY(dev_alloc(&c->d_raw, need));
+        c->norm_cap = 0;
         TRY(dev_alloc(&c->d_norm, need));
-        c->raw_cap = need;
+        c->norm_cap = need;
     }
     if (need_bits > c->bits_cap) {
         CU(cudaStreamSynchronize(c->stream));
@@ -606,6 +616,10 @@ static int direct_out_launch(yoda_ctx *c) {
     ppc = std::min(ppc, 64u);
     ppc = std::max(ppc, (P + 65534u) / 65535u);
     dim3 grid(gx, (P + ppc - 1) / ppc);
+    if (full) {
+        TRY(ensure_raw(c, (size_t)P * c->stride * sizeof(i64)));  // a YODA_EVAL_RAW32 batch that fell back to these kernels
+        c->res_raw32 = false;
+    }
     if (full)
         k_direct_out<true><<<grid, DCT, 0, st>>>(c->snap, c->d_pods, P, ppc, c->d_max6, c->d_count, c->d_hilo, c->d_ckey, c->d_raw,
                                                  c->d_norm, c->d_bits, c->stride);
@@ -724,11 +738,16 @@ static int fast_out_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     const u32 tiles = (c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32);
     const u32 chunk = hot_chunk(p_end - p_begin, tiles, c->out_slots);
     const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
-    if (c->ph_flags & YODA_EVAL_FULL)
-        k_fast_out<4, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
-                                                                 c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride, chunk);
+    const bool full = (c->ph_flags & YODA_EVAL_FULL) != 0;
+    if (full) c->res_raw32 = (c->ph_flags & YODA_EVAL_RAW32) != 0;
+    if (full && c->res_raw32)
+        k_fast_out<4, true, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
+                                                                       c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride, chunk);
+    else if (full)
+        k_fast_out<4, true, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
+                                                                        c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride, chunk);
     else
-        k_fast_out<4, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
+        k_fast_out<4, false, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
                                                                   c->d_ckey, nullptr, nullptr, nullptr, c->stride, chunk);
     LAUNCHED(c);
     return YODA_OK;
@@ -865,8 +884,9 @@ static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
     if (P > (1u << 22)) return fail(YODA_E_RANGE, "batch of %u pods exceeds the limit of %u per call; split it", P, 1u << 22);
     TRY(ensure_pods(c, P));
     c->stride = round_up(std::max(c->snap.n_nodes, 1u), 1024);  // rows padded to the hot kernels' CTA tile
-    if (flags & YODA_EVAL_FULL) TRY(ensure_matrices(c, P, c->stride));
+    if (flags & ~(YODA_EVAL_FULL | YODA_EVAL_FORCE_DIRECT | YODA_EVAL_RAW32)) return fail(YODA_E_ARG, "unknown evaluation flags 0x%x", flags);
     c->ph_path = (c->narrow_ok && !(flags & YODA_EVAL_FORCE_DIRECT)) ? 1 : 0;
+    if (flags & YODA_EVAL_FULL) TRY(ensure_matrices(c, P, c->stride, (c->ph_path == 1 && (flags & YODA_EVAL_RAW32)) ? 4u : 8u));
     if (c->ph_path == 1) TRY(ensure_fast(c, P));
     c->ph_P = P;
     c->ph_flags = flags;
@@ -1097,7 +1117,17 @@ extern "C" int yoda_fetch_row(yoda_ctx *c, u32 pod, int kind, void *dst, size_t 
     size_t row;
     switch (kind) {
         case YODA_ROW_FEASIBLE_BITS: src = c->d_bits + (size_t)pod * (c->stride / 32); row = (c->stride / 32) * 4; break;
-        case YODA_ROW_RAW: src = c->d_raw + (size_t)pod * c->stride; row = c->stride * 8; break;
+        case YODA_ROW_RAW:
+            if (c->res_raw32) {  // uint32 on the device, int64 for the caller
+                if (bytes > c->stride * 8) return fail(YODA_E_RANGE, "row kind %d holds %zu bytes, %zu requested", kind, (size_t)c->stride * 8, bytes);
+                const size_t n = bytes / 8;
+                std::vector<u32> tmp(n);
+                CU(cudaMemcpyAsync(tmp.data(), (const u32 *)c->d_raw + (size_t)pod * c->stride, n * 4, cudaMemcpyDeviceToHost, c->stream));
+                CU(cudaStreamSynchronize(c->stream));
+                for (size_t i = 0; i < n; ++i) ((i64 *)dst)[i] = (i64)tmp[i];
+                return YODA_OK;
+            }
+            src = c->d_raw + (size_t)pod * c->stride; row = c->stride * 8; break;
         case YODA_ROW_NORM: src = c->d_norm + (size_t)pod * c->stride; row = c->stride; break;
         default: return fail(YODA_E_ARG, "unknown row kind %d", kind);
     }
@@ -1115,6 +1145,14 @@ extern "C" int yoda_result_matrices(yoda_ctx *c, void **d_bits, void **d_raw, vo
     if (d_raw) *d_raw = c->d_raw;
     if (d_norm) *d_norm = c->d_norm;
     if (stride) *stride = c->stride;
+    return YODA_OK;
+}
+
+extern "C" int yoda_result_raw_bytes(yoda_ctx *c, uint32_t *bytes) {
+    if (!c || !bytes) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!c->last_full) return fail(YODA_E_STATE, "no YODA_EVAL_FULL result");
+    *bytes = c->res_raw32 ? 4u : 8u;
     return YODA_OK;
 }
 
