@@ -91,7 +91,8 @@ func (c *Ctx) Eval(pods []PodReq, full bool) ([]PodResult, error) {
 	}
 	flags := C.uint32_t(C.YODA_EVAL_DECIDE)
 	if full {
-		flags = C.uint32_t(C.YODA_EVAL_FULL)
+		// rows are only ever read through yoda_fetch_row (int64 either way): let the device keep the scores as uint32
+		flags = C.uint32_t(C.YODA_EVAL_FULL | C.YODA_EVAL_RAW32)
 	}
 	rc := C.yoda_eval_batch(c.h, (*C.yoda_pod_req)(unsafe.Pointer(&pods[0])), C.uint32_t(len(pods)), flags,
 		(*C.yoda_pod_result)(unsafe.Pointer(&out[0])))
