@@ -678,6 +678,7 @@ struct ScoreSmem {
     __align__(16) u32 lo_s[HOT_WARPS][HOT_CHUNK];
     __align__(16) u32 cnt_s[HOT_WARPS][HOT_CHUNK];   // DECIDE only: feasible nodes of the warp's slots
     __align__(16) u32 best_s[HOT_WARPS][HOT_CHUNK];  // DECIDE only: lowest node index holding the warp's top score
+    u32 mark_s[HOT_WARPS][HOT_CHUNK / 32];           // bit i: the warp's entry for pod i is set (it holds until the next set bit)
 };
 
 // score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145).
@@ -730,75 +731,79 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
     u32 hi_l[NPL], lo_l[NPL], bound[NPL];
 #pragma unroll
     for (int j = 0; j < NPL; ++j) { hi_l[j] = 0; lo_l[j] = 0xFFFFFFFFu; bound[j] = 0; }
-    u32 hi_w = 0, lo_w = 0xFFFFFFFFu, bmin = 0;  // bmin = min over the lane's slots of bound[j]
-    u32 cnt_w = 0, best_w = 0xFFFFFFFFu;
-    for (u32 i0 = 0; i0 < cn; i0 += SCORE_BLK) {
-        const uint4 bs = sm.blk[i0 / SCORE_BLK];
-        if (bs.x == cur_gid && bs.y == cur_cls && bs.z >= cur_m && !__any_sync(0xFFFFFFFFu, bs.w > bmin)) {
-            cur_m = bs.w;
-            if (lane == 0) {
-                *reinterpret_cast<uint4 *>(&sm.hi_s[warp][i0]) = make_uint4(hi_w, hi_w, hi_w, hi_w);
-                *reinterpret_cast<uint4 *>(&sm.lo_s[warp][i0]) = make_uint4(lo_w, lo_w, lo_w, lo_w);
-                if (DECIDE) {
-                    *reinterpret_cast<uint4 *>(&sm.cnt_s[warp][i0]) = make_uint4(cnt_w, cnt_w, cnt_w, cnt_w);
-                    *reinterpret_cast<uint4 *>(&sm.best_s[warp][i0]) = make_uint4(best_w, best_w, best_w, best_w);
-                }
+    u32 bmin = 0;  // min over the lane's slots of bound[j]
+    // A warp's (highest, lowest) only changes when one of its slots is re-evaluated, so it is stored for those
+    // pods alone, with a mark bit; a pod without a mark takes the entry of the last marked pod before it.  The
+    // cache-hit path therefore writes nothing at all.  Marks are kept per window of 32 pods.
+    for (u32 w0 = 0; w0 < HOT_CHUNK; w0 += 32) {
+        u32 mk = 0;
+        const u32 w1 = min(cn, w0 + 32);
+        for (u32 i0 = w0; i0 < w1; i0 += SCORE_BLK) {
+            const uint4 bs = sm.blk[i0 / SCORE_BLK];
+            if (bs.x == cur_gid && bs.y == cur_cls && bs.z >= cur_m && !__any_sync(0xFFFFFFFFu, bs.w > bmin)) {
+                cur_m = bs.w;
+                continue;
             }
-            continue;
-        }
-        const u32 i1 = min(cn, i0 + SCORE_BLK);
-        for (u32 i = i0; i < i1; ++i) {
-            const PodRegs pod = pod_from_smem(sm.sp, i);
-            const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
-            if (!same || __any_sync(0xFFFFFFFFu, pod.m > bmin)) {
-                cur_cls = pod.cls; cur_gid = pod.gid;
+            const u32 i1 = min(cn, i0 + SCORE_BLK);
+            for (u32 i = i0; i < i1; ++i) {
+                const PodRegs pod = pod_from_smem(sm.sp, i);
+                const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
+                if (!same || __any_sync(0xFFFFFFFFu, pod.m > bmin)) {
+                    cur_cls = pod.cls; cur_gid = pod.gid;
 #pragma unroll
-                for (int j = 0; j < NPL; ++j) {
-                    if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
-                        bool fit;
-                        u32 b;
-                        const u32 raw = hot_eval_mem(s, tables, node[j], pod.cls, pod.m, pod.num, pod.reqM, pod.has_clock, pod.c, pod.reqC, ok[j],
-                                                     cardnum[j], stat[j], fit, b);
-                        bound[j] = fit ? b : 0xFFFFFFFFu;
-                        hi_l[j] = fit ? raw : 0u;
-                        lo_l[j] = fit ? raw : 0xFFFFFFFFu;
+                    for (int j = 0; j < NPL; ++j) {
+                        if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
+                            bool fit;
+                            u32 b;
+                            const u32 raw = hot_eval_mem(s, tables, node[j], pod.cls, pod.m, pod.num, pod.reqM, pod.has_clock, pod.c, pod.reqC, ok[j],
+                                                         cardnum[j], stat[j], fit, b);
+                            bound[j] = fit ? b : 0xFFFFFFFFu;
+                            hi_l[j] = fit ? raw : 0u;
+                            lo_l[j] = fit ? raw : 0xFFFFFFFFu;
+                        }
+                    }
+                    u32 hi = hi_l[0], lo = lo_l[0];
+                    bmin = bound[0];
+#pragma unroll
+                    for (int j = 1; j < NPL; ++j) { hi = max(hi, hi_l[j]); lo = min(lo, lo_l[j]); bmin = min(bmin, bound[j]); }
+                    const u32 hi_w = __reduce_max_sync(0xFFFFFFFFu, hi);
+                    const u32 lo_w = __reduce_min_sync(0xFFFFFFFFu, lo);
+                    u32 cnt_w = 0, best_w = 0xFFFFFFFFu;
+                    if (DECIDE) {
+#pragma unroll
+                        for (int j = NPL - 1; j >= 0; --j) {
+                            const bool fitj = lo_l[j] != 0xFFFFFFFFu;
+                            cnt_w += __popc(__ballot_sync(0xFFFFFFFFu, fitj));
+                            const u32 top = __ballot_sync(0xFFFFFFFFu, fitj && hi_l[j] == hi_w);
+                            if (top) best_w = base + j * 32 + (__ffs(top) - 1);
+                        }
+                    }
+                    mk |= 1u << (i - w0);
+                    if (lane == 0) {
+                        sm.hi_s[warp][i] = hi_w;
+                        sm.lo_s[warp][i] = lo_w;
+                        if (DECIDE) {
+                            sm.cnt_s[warp][i] = cnt_w;
+                            sm.best_s[warp][i] = best_w;
+                        }
                     }
                 }
-                u32 hi = hi_l[0], lo = lo_l[0];
-                bmin = bound[0];
-#pragma unroll
-                for (int j = 1; j < NPL; ++j) { hi = max(hi, hi_l[j]); lo = min(lo, lo_l[j]); bmin = min(bmin, bound[j]); }
-                hi_w = __reduce_max_sync(0xFFFFFFFFu, hi);
-                lo_w = __reduce_min_sync(0xFFFFFFFFu, lo);
-                if (DECIDE) {
-                    cnt_w = 0; best_w = 0xFFFFFFFFu;
-#pragma unroll
-                    for (int j = NPL - 1; j >= 0; --j) {
-                        const bool fitj = lo_l[j] != 0xFFFFFFFFu;
-                        cnt_w += __popc(__ballot_sync(0xFFFFFFFFu, fitj));
-                        const u32 top = __ballot_sync(0xFFFFFFFFu, fitj && hi_l[j] == hi_w);
-                        if (top) best_w = base + j * 32 + (__ffs(top) - 1);
-                    }
-                }
-            }
-            cur_m = pod.m;
-            if (lane == 0) {
-                sm.hi_s[warp][i] = hi_w;
-                sm.lo_s[warp][i] = lo_w;
-                if (DECIDE) {
-                    sm.cnt_s[warp][i] = cnt_w;
-                    sm.best_s[warp][i] = best_w;
-                }
+                cur_m = pod.m;
             }
         }
+        if (lane == 0) sm.mark_s[warp][w0 >> 5] = mk;
     }
     half_sync(bar_id);
     for (u32 i = tid; i < cn; i += HOT_THREADS) {
-        u32 hi = 0, lo = 0xFFFFFFFFu;
+        u32 hi = 0, lo = 0xFFFFFFFFu, q[HOT_WARPS];
 #pragma unroll
         for (int w = 0; w < HOT_WARPS; ++w) {
-            hi = max(hi, sm.hi_s[w][i]);
-            lo = min(lo, sm.lo_s[w][i]);
+            // the warp's entry for pod i sits at the last marked pod at or before i (pod 0 of a chunk is always marked)
+            u32 k = i >> 5, m = sm.mark_s[w][k] & (0xFFFFFFFFu >> (31 - (i & 31)));
+            while (!m && k) m = sm.mark_s[w][--k];
+            q[w] = (k << 5) + (31 - __clz(m | 1u));
+            hi = max(hi, sm.hi_s[w][q[w]]);
+            lo = min(lo, sm.lo_s[w][q[w]]);
         }
         if (lo != 0xFFFFFFFFu) {  // some node of this tile is feasible
             const u32 orig = sm.sp[2 * i + 1].y;
@@ -808,8 +813,8 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
                 u32 cnt = 0, best = 0xFFFFFFFFu;
 #pragma unroll
                 for (int w = HOT_WARPS - 1; w >= 0; --w) {  // warps hold ascending node ranges: the last match wins = lowest index
-                    cnt += sm.cnt_s[w][i];
-                    if (sm.cnt_s[w][i] && sm.hi_s[w][i] == hi) best = sm.best_s[w][i];
+                    cnt += sm.cnt_s[w][q[w]];
+                    if (sm.cnt_s[w][q[w]] && sm.hi_s[w][q[w]] == hi) best = sm.best_s[w][q[w]];
                 }
                 atomicAdd(&count[orig], (u64)cnt);
                 atomicMax(&dkey[orig], ((u64)hi << 32) | (u64)(0xFFFFFFFFu - (s.node_base + best)));
