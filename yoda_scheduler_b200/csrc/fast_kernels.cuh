@@ -537,7 +537,10 @@ __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__r
 // ------------------------------------------------------------------------------------------
 #define HOT_THREADS 256
 #define HOT_WARPS (HOT_THREADS / 32)
-#define HOT_CHUNK 128  // pods per CTA
+#define HOT_CHUNK 128  // pods per CTA of the output pass
+#ifndef SCORE_CHUNK
+#define SCORE_CHUNK 256  // pods per CTA of the score pass: every chunk starts with a full evaluation of the CTA's nodes
+#endif
 
 template <int NPL>
 struct NodeRegs {
@@ -672,13 +675,13 @@ __device__ __forceinline__ void half_sync(int bar_id) { asm volatile("bar.sync %
 
 #define SCORE_BLK 4
 struct ScoreSmem {
-    uint4 sp[HOT_CHUNK * 2];
-    uint4 blk[HOT_CHUNK / SCORE_BLK];  // gid (or ~0 if mixed), cls, first m, last m of four consecutive pods
-    __align__(16) u32 hi_s[HOT_WARPS][HOT_CHUNK];
-    __align__(16) u32 lo_s[HOT_WARPS][HOT_CHUNK];
-    __align__(16) u32 cnt_s[HOT_WARPS][HOT_CHUNK];   // DECIDE only: feasible nodes of the warp's slots
-    __align__(16) u32 best_s[HOT_WARPS][HOT_CHUNK];  // DECIDE only: lowest node index holding the warp's top score
-    u32 mark_s[HOT_WARPS][HOT_CHUNK / 32];           // bit i: the warp's entry for pod i is set (it holds until the next set bit)
+    uint4 sp[SCORE_CHUNK * 2];
+    uint4 blk[SCORE_CHUNK / SCORE_BLK];  // gid (or ~0 if mixed), cls, first m, last m of four consecutive pods
+    __align__(16) u32 hi_s[HOT_WARPS][SCORE_CHUNK];
+    __align__(16) u32 lo_s[HOT_WARPS][SCORE_CHUNK];
+    __align__(16) u32 cnt_s[HOT_WARPS][SCORE_CHUNK];   // DECIDE only: feasible nodes of the warp's slots
+    __align__(16) u32 best_s[HOT_WARPS][SCORE_CHUNK];  // DECIDE only: lowest node index holding the warp's top score
+    u32 mark_s[HOT_WARPS][SCORE_CHUNK / 32];           // bit i: the warp's entry for pod i is set (it holds until the next set bit)
 };
 
 // score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145).
@@ -709,7 +712,7 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
         ok[j] = in && (s.meta[node[j]] & META_HAS_SCV);
     }
     half_sync(bar_id);
-    if (tid < HOT_CHUNK / SCORE_BLK) {
+    if (tid < SCORE_CHUNK / SCORE_BLK) {
         const u32 b0 = tid * SCORE_BLK;
         uint4 v = make_uint4(0xFFFFFFFFu, 0, 0, 0);
         if (b0 + SCORE_BLK <= cn) {
@@ -735,7 +738,7 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
     // A warp's (highest, lowest) only changes when one of its slots is re-evaluated, so it is stored for those
     // pods alone, with a mark bit; a pod without a mark takes the entry of the last marked pod before it.  The
     // cache-hit path therefore writes nothing at all.  Marks are kept per window of 32 pods.
-    for (u32 w0 = 0; w0 < HOT_CHUNK; w0 += 32) {
+    for (u32 w0 = 0; w0 < SCORE_CHUNK; w0 += 32) {
         u32 mk = 0;
         const u32 w1 = min(cn, w0 + 32);
         for (u32 i0 = w0; i0 < w1; i0 += SCORE_BLK) {
@@ -974,7 +977,7 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
 template <int NPL, bool DECIDE>
 __global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
                                                             const u32 *__restrict__ tables, u64 *hilo, u64 *count, u64 *dkey,
-                                                            u32 chunk_pods) {  // pods per CTA: a multiple of SCORE_BLK, <= HOT_CHUNK
+                                                            u32 chunk_pods) {  // pods per CTA: a multiple of SCORE_BLK, <= SCORE_CHUNK
     __shared__ ScoreSmem sm;
     score_body<NPL, DECIDE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo, count, dkey, chunk_pods);
 }

@@ -706,21 +706,21 @@ static int fast_phase0(yoda_ctx *c) {
     return YODA_OK;
 }
 
-// Pods per CTA of the two hot kernels.  HOT_CHUNK for big batches; for small and medium ones the last wave of CTAs
+// Pods per CTA of the two hot kernels.  The maximum for big batches; for small and medium ones the last wave of CTAs
 // would be mostly empty, so the chunk shrinks until the CTAs fill whole waves (slots = CTAs resident at once).
-static u32 hot_chunk(u32 n_pods, u32 tiles, u32 slots) {
-    const u32 chunks = (n_pods + HOT_CHUNK - 1) / HOT_CHUNK;
+static u32 hot_chunk(u32 n_pods, u32 tiles, u32 slots, u32 max_chunk) {
+    const u32 chunks = (n_pods + max_chunk - 1) / max_chunk;
     const u32 waves = (tiles * chunks + slots - 1) / slots;
     const u32 want = std::max(chunks, waves * slots / std::max(tiles, 1u));  // chunks that still fit those waves
     u32 chunk = (n_pods + want - 1) / want;
-    chunk = std::min<u32>(HOT_CHUNK, std::max<u32>(16u, (chunk + SCORE_BLK - 1) / SCORE_BLK * SCORE_BLK));
+    chunk = std::min<u32>(max_chunk, std::max<u32>(16u, (chunk + SCORE_BLK - 1) / SCORE_BLK * SCORE_BLK));
     return chunk;
 }
 
 static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
     const u32 tiles = (c->snap.n_nodes + HOT_WARPS * SCORE_NPL * 32 - 1) / (HOT_WARPS * SCORE_NPL * 32);
-    const u32 chunk = hot_chunk(p_end - p_begin, tiles, c->score_slots);
+    const u32 chunk = hot_chunk(p_end - p_begin, tiles, c->score_slots, SCORE_CHUNK);
     const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
     if (c->fw_decide_merged)
         k_fast_score<SCORE_NPL, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
@@ -736,7 +736,7 @@ static int fast_out_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
     constexpr int NPL = 4;
     const u32 tiles = (c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32);
-    const u32 chunk = hot_chunk(p_end - p_begin, tiles, c->out_slots);
+    const u32 chunk = hot_chunk(p_end - p_begin, tiles, c->out_slots, HOT_CHUNK);
     const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
     const bool full = (c->ph_flags & YODA_EVAL_FULL) != 0;
     if (full) c->res_raw32 = (c->ph_flags & YODA_EVAL_RAW32) != 0;
