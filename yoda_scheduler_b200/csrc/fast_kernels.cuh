@@ -975,7 +975,7 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
 }
 
 template <int NPL, bool DECIDE>
-__global__ void __launch_bounds__(HOT_THREADS) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
+__global__ void __launch_bounds__(HOT_THREADS, 4) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
                                                             const u32 *__restrict__ tables, u64 *hilo, u64 *count, u64 *dkey,
                                                             u32 chunk_pods) {  // pods per CTA: a multiple of SCORE_BLK, <= SCORE_CHUNK
     __shared__ ScoreSmem sm;
