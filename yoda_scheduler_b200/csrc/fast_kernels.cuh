@@ -8,11 +8,11 @@
 //     (group, memory);
 //  2. collection.CollectMaxValues becomes a 1-D dominance problem per group: a card counts for a
 //     pod iff memory <= e(card) with e = min(FreeMemory, k-th largest healthy FreeMemory of its
-//     node), so each card binary-searches the group's sorted memory values once and a suffix-max
-//     scan over the pods finishes the six maxima -- O((cards + pods) log pods) per group instead
-//     of O(pods x cards);
+//     node), so each card that no other card of its node dominates searches the group's sorted
+//     memory values once and a suffix-max scan over the pods finishes the six maxima --
+//     O((cards + pods) log pods) per group instead of O(pods x cards);
 //  3. pods with the same six maxima form a class; per class a table of per-card scores
-//     (algorithm.go:57-68, six real divisions) is built once per batch;
+//     (algorithm.go:57-68, the six divisions taken with the class's reciprocals) is built once per batch;
 //  4. the two hot kernels (score reduce, output pass) run lane = node with the node's eight
 //     FreeMemory values and eight class card scores in registers and loop over the sorted pods:
 //     one compare + one predicated add per card, the healthy-card count for Filter riding in
@@ -203,7 +203,7 @@ __global__ void k_build_sorted(const PodC *__restrict__ pods, u32 P, const u64 *
 // ------------------------------------------------------------------------------------------
 // step 2: CollectMaxValues as dominance queries.  thread = (node, group).
 // step[f][i] (sorted pod position i) receives the maxima of the cards whose LAST admissible pod is i;
-// k_max_scan turns that into the maxima of all cards admissible for pod i.
+// k_max_tile_lead + k_max_scan turn that into the maxima of all cards admissible for pod i.
 // ------------------------------------------------------------------------------------------
 #define MAXT 128
 #define MAXG_TILE 8  // group descriptors staged per shared-memory tile
