@@ -478,3 +478,39 @@ def test_raw32_request_survives_a_fallback():
         ctx.load_snapshot(snap)
         with pytest.raises(api.YodaError):
             ctx.eval(pods_to_requests(labels), 64)          # unknown flag bits are rejected
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_heterogeneous_cards_medium(seed):
+    """Nodes whose cards differ in every field (so several cards per node survive the dominance pruning of
+    the maxima pass, and nodes of one warp disagree on clock tests), many requirement groups, on the fast
+    path: every output against the oracle."""
+    rng = random.Random(900 + seed)
+    N, P = 1500, 2500
+    clocks = [877, 1215, 1410, 5705, 7000]
+    nodes = []
+    for i in range(N):
+        nc = rng.choice([1, 2, 4, 8, 8])
+        cards = []
+        for g in range(nc):
+            total = rng.choice([8000, 11000, 16000, 24000, 40536, 81920])
+            cards.append({"health": "Healthy" if rng.random() > 0.08 else "Unhealthy", "free": rng.randrange(total + 1), "total": total,
+                          "clock": rng.choice(clocks), "core": rng.choice([2560, 3584, 4352, 5120, 6912]),
+                          "bandwidth": rng.choice([320, 352, 448, 616, 900, 1555]), "power": rng.choice([70, 250, 260, 300, 400])})
+        running = [{"scv/memory": str(rng.randrange(100, 30000))} for _ in range(rng.randrange(0, 3))]
+        nodes.append({"name": f"n{i}", "has_scv": rng.random() > 0.02, "card_number": rng.choice([nc, nc, nc, 8, 0]), "cards": cards,
+                      "free_sum": sum(c["free"] for c in cards), "total_sum": sum(c["total"] for c in cards), "pods": running})
+    labels = []
+    for _ in range(P):
+        d = {}
+        if rng.random() < 0.6:
+            d["scv/number"] = str(rng.choice([0, 1, 1, 2, 2, 3, 4, 8, 9]))
+        if rng.random() < 0.8:
+            d["scv/memory"] = str(rng.randrange(1, 82000))
+        if rng.random() < 0.4:
+            d["scv/clock"] = str(rng.choice(clocks + [999]))
+        labels.append(d)
+    snap = Snapshot.from_nodes(nodes)
+    res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_FULL)
+    assert t.path == 1 and t.n_groups > 60
+    assert_matches_oracle(snap, labels, res, mats, what=f"heterogeneous seed={seed}")
