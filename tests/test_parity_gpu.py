@@ -514,3 +514,35 @@ def test_heterogeneous_cards_medium(seed):
     res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_FULL)
     assert t.path == 1 and t.n_groups > 60
     assert_matches_oracle(snap, labels, res, mats, what=f"heterogeneous seed={seed}")
+
+
+def test_cluster_grows_and_cards_are_replaced():
+    """Between two cycles the cluster gains nodes and some nodes get different cards (other clocks, cores,
+    memory sizes): everything derived at commit -- narrow planes, node order by clock, surviving cards,
+    k-th largest FreeMemory -- has to follow.  Checked against a fresh context and the oracle."""
+    N0, N1, P = 1000, 1500, 600
+    final = synth.make_snapshot(N1)
+    other = synth.make_snapshot(N1, seed=synth.SEED + 9)     # same shapes, different SKUs per node
+    reqs = synth.make_requests(P, 41)
+    labels = synth.make_pod_labels(P, 41)
+    with api.Context(N1) as ctx:
+        first = np.arange(N0)
+        live = first[other.has_scv[first] == 1]
+        ctx.upsert_many(live, other.records(live))            # cycle 1 sees the "other" cards on nodes 0..N0-1
+        ctx.commit()
+        assert ctx.node_count() == int(live.max()) + 1
+        ctx.eval(reqs, api.EVAL_FULL)
+        assert ctx.timing().path == 1
+        ctx.load_snapshot(final)                              # replace every node's cards, add nodes N0..N1-1
+        got = ctx.eval(reqs, api.EVAL_FULL)
+        got_m = ctx.fetch_all(P)
+        assert ctx.timing().path == 1
+    with api.Context(N1) as fresh:
+        fresh.load_snapshot(final)
+        want = fresh.eval(reqs, api.EVAL_FULL)
+        want_m = fresh.fetch_all(P)
+    assert got_m["raw"].shape == want_m["raw"].shape
+    assert np.array_equal(got, want)
+    for k in got_m:
+        assert np.array_equal(got_m[k], want_m[k]), k
+    assert_matches_oracle(final, labels, got, got_m, what="grown cluster")
