@@ -65,7 +65,25 @@ def test_shards_on_one_gpu_equal_single(n_shards, flags):
         c.close()
 
 
+def _widen(snap, lo):
+    """Give the first node at or after `lo` that has an SCV a CardNumber beyond 32 bits: its shard leaves the narrow
+    fast path, the other shards do not (a wide card field would travel to them through the maxima)."""
+    node = lo + int(np.nonzero(snap.has_scv[lo:] == 1)[0][0])
+    snap.card_number[node] = np.uint64(1) << np.uint64(40)
+
+
 def _nccl_worker(rank, world, port, N, P, out_dir):
+    try:
+        _nccl_worker_body(rank, world, port, N, P, out_dir)
+    except BaseException:   # a rank that dies quietly leaves the other one waiting in a collective for minutes
+        import traceback
+        traceback.print_exc()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(1)
+
+
+def _nccl_worker_body(rank, world, port, N, P, out_dir):
     sys.path.insert(0, ROOT)
     import torch
     import torch.distributed as dist
@@ -76,12 +94,24 @@ def _nccl_worker(rank, world, port, N, P, out_dir):
     per = N // world
     ctx = api.Context(per, device=rank, node_base=rank * per, shard_rank=rank, shard_count=world)
     shard.init_nccl(ctx, rank, world, dev)
-    ctx.load_snapshot(synth.make_snapshot(per, node_offset=rank * per))
+    snap = synth.make_snapshot(per, node_offset=rank * per)
+    ctx.load_snapshot(snap)
     reqs = synth.make_requests(P, 31)
     res = ctx.eval(reqs, api.EVAL_FULL)                       # exchanges run inside the library (NCCL)
     res2 = shard.eval_host_driven(ctx, reqs, api.EVAL_FULL, dev)   # same through torch.distributed
     assert np.array_equal(res, res2)
     np.save(os.path.join(out_dir, f"res{rank}.npy"), res)
+    # DECIDE: every shard is on the table path, so they agree on the one-pass variant (choices out of the score pass)
+    dec = ctx.eval(reqs, api.EVAL_DECIDE)
+    assert ctx.timing().path == 1
+    np.save(os.path.join(out_dir, f"dec{rank}.npy"), dec)
+    # DECIDE with one shard on the exact kernels: the shards must agree on the two-pass protocol instead
+    if rank == 1:
+        _widen(snap, 0)
+        ctx.load_snapshot(snap)
+    mixed = ctx.eval(reqs, api.EVAL_DECIDE)
+    assert ctx.timing().path == (0 if rank == 1 else 1)
+    np.save(os.path.join(out_dir, f"mix{rank}.npy"), mixed)
     dist.barrier()
     ctx.close()
     dist.destroy_process_group()
@@ -95,11 +125,21 @@ def test_two_gpus_nccl(tmp_path):
     N, P, world = 4000, 600, 2
     port = 29500 + os.getpid() % 2000
     mp.spawn(_nccl_worker, args=(world, port, N, P, str(tmp_path)), nprocs=world, join=True)
+    reqs = synth.make_requests(P, 31)
+    snap = synth.make_snapshot(N)
     with api.Context(N) as single:
-        single.load_snapshot(synth.make_snapshot(N))
-        want = single.eval(synth.make_requests(P, 31), api.EVAL_FULL)
+        single.load_snapshot(snap)
+        want = single.eval(reqs, api.EVAL_FULL)
+        want_dec = single.eval(reqs, api.EVAL_DECIDE)
+        assert np.array_equal(want, want_dec)
+        _widen(snap, N // world)
+        single.load_snapshot(snap)
+        want_mix = single.eval(reqs, api.EVAL_DECIDE)
+        assert single.timing().path == 0
     for r in range(world):
         assert np.array_equal(np.load(tmp_path / f"res{r}.npy"), want)
+        assert np.array_equal(np.load(tmp_path / f"dec{r}.npy"), want)
+        assert np.array_equal(np.load(tmp_path / f"mix{r}.npy"), want_mix)
 
 
 def test_pod_sharding_equals_single():

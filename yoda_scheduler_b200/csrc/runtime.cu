@@ -136,6 +136,8 @@ struct yoda_ctx {
     u32 list_cap = 0;
     // NCCL
     ncclComm_t comm = nullptr;
+    u64 *d_agree = nullptr, *h_agree = nullptr;  // one word all-reduced before a sharded DECIDE score pass (see phase1)
+    bool fw_agree = false;                       // this evaluation may ask the other shards which kernels they run
     // fast (narrow) path workspace
     int ph_path = 0;  // path of the evaluation in flight: 0 direct, 1 fast
     u32 fw_pods_cap = 0, fw_htab = 0;
@@ -292,6 +294,8 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     DeviceGuard dg(c->cfg.device);
     cudaDeviceSynchronize();
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    dev_free(c->d_agree);
+    if (c->h_agree) cudaFreeHost(c->h_agree);
     DevSnap &s = c->snap;
     for (int f = 0; f < NFIELD; ++f) dev_free(s.f[f]);
     dev_free(s.card_number); dev_free(s.free_sum); dev_free(s.total_sum); dev_free(s.alloc_sum);
@@ -855,6 +859,18 @@ static int phase0(yoda_ctx *c, const yoda_pod_req *d_req) {
 // phase 1: local lowest/highest over feasible nodes
 static int phase1(yoda_ctx *c) {
     if (c->ph_path == 1) TRY(fast_classes(c));
+    if (c->fw_agree) {
+        // Sharded DECIDE: the one-pass variant (choices out of the score pass, one exchange less, no output pass)
+        // packs the choice key differently from the exact kernels, so it is used only if every shard runs the
+        // table path -- which a shard knows for itself only now.  One word, all-reduced with MAX: 1 = "I do not".
+        cudaStream_t st = c->stream;
+        CU(cudaMemsetAsync(c->d_agree, 0, sizeof(u64), st));
+        if (c->ph_path != 1) CU(cudaMemsetAsync(c->d_agree, 1, 1, st));  // little-endian: the word becomes 1
+        NC(g_nccl.AllReduce(c->d_agree, c->d_agree, 1, ncclUint64, ncclMax, c->comm, st));
+        CU(cudaMemcpyAsync(c->h_agree, c->d_agree, sizeof(u64), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        c->fw_decide_merged = (*c->h_agree == 0);
+    }
     if (c->ph_path == 0) c->fw_decide_merged = false;
     if (c->ph_path == 1) TRY(fast_score_launch(c, 0, c->ph_P));
     if (c->ph_path == 0) TRY(direct_pods_launch(c, 1));
@@ -903,8 +919,14 @@ static int exchange_locked(yoda_ctx *c, int phase) {
     if (phase == 0) {
         NC(g_nccl.AllReduce(c->d_max6, c->d_max6, (size_t)P * 6, ncclUint64, ncclMax, c->comm, c->stream));
     } else if (phase == 1) {
+        NC(g_nccl.GroupStart());
         NC(g_nccl.AllReduce(c->d_hilo, c->d_hilo, (size_t)P * 2, ncclUint64, ncclMax, c->comm, c->stream));
-    } else if (phase == 2) {
+        if (c->fw_decide_merged) {  // agreed on by all shards in phase1: choice keys and counts are ready too
+            NC(g_nccl.AllReduce(c->d_ckey, c->d_ckey, P, ncclUint64, ncclMax, c->comm, c->stream));
+            NC(g_nccl.AllReduce(c->d_count, c->d_count, P, ncclUint64, ncclSum, c->comm, c->stream));
+        }
+        NC(g_nccl.GroupEnd());
+    } else if (phase == 2 && !c->fw_decide_merged) {
         NC(g_nccl.GroupStart());
         NC(g_nccl.AllReduce(c->d_ckey, c->d_ckey, P, ncclUint64, ncclMax, c->comm, c->stream));
         NC(g_nccl.AllReduce(c->d_count, c->d_count, P, ncclUint64, ncclSum, c->comm, c->stream));
@@ -936,6 +958,7 @@ static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
     c->fw_allow_defer = (c->comm == nullptr);
     c->fw_deferred_err = false;
     c->fw_decide_merged = (c->comm == nullptr) && !(c->ph_flags & YODA_EVAL_FULL) && c->ph_path == 1;
+    c->fw_agree = (c->comm != nullptr) && !(c->ph_flags & YODA_EVAL_FULL);
     TRY(phase0(c, d_req));
     TRY(exchange_locked(c, 0));
     TRY(phase1(c));
@@ -944,6 +967,7 @@ static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
     TRY(exchange_locked(c, 2));
     TRY(phase3(c));
     c->fw_allow_defer = false;
+    c->fw_agree = false;
     c->ph_done = 3;
     c->last_P = c->ph_P;
     c->last_full = (c->ph_flags & YODA_EVAL_FULL) != 0;
@@ -1167,6 +1191,7 @@ extern "C" int yoda_phase_begin(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u3
     c->fw_allow_defer = false;
     c->fw_deferred_err = false;
     c->fw_decide_merged = false;
+    c->fw_agree = false;
     c->fw_groups_pending = false;
     CU(cudaMemcpyAsync(c->d_req, pods, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));  // caller's buffer may be pageable and is not retained
@@ -1354,5 +1379,9 @@ extern "C" int yoda_comm_init(yoda_ctx *c, const void *id128, u32 rank, u32 n_ra
     ncclUniqueId id;
     memcpy(&id, id128, sizeof id);
     NC(g_nccl.CommInitRank(&c->comm, (int)n_ranks, id, (int)rank));
+    if (!c->d_agree) {
+        TRY(dev_alloc(&c->d_agree, 1));
+        if (cudaMallocHost((void **)&c->h_agree, sizeof(u64)) != cudaSuccess) return fail(YODA_E_NOMEM, "cudaMallocHost of the agreement word failed");
+    }
     return YODA_OK;
 }
