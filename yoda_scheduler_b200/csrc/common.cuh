@@ -3,7 +3,7 @@
 // Device snapshot ("wide planes", the source of truth in HBM): one plane per scv.Card field,
 // node-major with the YODA_MAX_CARDS card slots of a node contiguous, uint64 so that every
 // value the reference can hold (Go uint/uint64) is representable.  Narrow uint32 planes for
-// the fast path are derived from these by k_prepare at commit time.
+// the fast path are derived from these, node by node, right after an update is scattered (k_prepare_updates).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -20,6 +20,7 @@ typedef uint8_t u8;
 
 // node meta word: bits 0-7 healthy mask, bits 8-11 n_cards, bit 16 has_scv
 #define META_HAS_SCV 0x10000u
+#define META_WIDE 0x20000u  // derived: the node (with an SCV) has a value outside the narrow range; counted in the snapshot-wide verdict
 // bits 24-31 (derived at commit): cards that no other card of the node dominates in all six fields -- the only ones
 // CollectMaxValues can ever take a maximum from
 __host__ __device__ __forceinline__ u32 meta_keep(u32 m) { return m >> 24; }

@@ -34,26 +34,24 @@ __global__ void k_scatter_updates(DevSnap s, const UpdRec *__restrict__ upd, u32
             s.total_sum[n] = u.rec.total_memory_sum;
             const u32 nc = u.rec.n_cards;
             const u32 hm = u.rec.healthy_mask & ((1u << nc) - 1u) & 0xFFu;
-            s.meta[n] = META_HAS_SCV | (nc << 8) | hm;
+            s.meta[n] = META_HAS_SCV | (nc << 8) | hm | (s.meta[n] & META_WIDE);  // the derive step below settles the wide bit
         }
     }
     if (g == 0) {
         if (u.op & UPD_ALLOC) s.alloc_sum[n] = u.alloc;
-        if (u.op & UPD_REMOVE) s.meta[n] = 0;
+        if (u.op & UPD_REMOVE) s.meta[n] &= META_WIDE;
     }
 }
 
-// Derived per-node data, recomputed for every node at commit:
+// Derived per-node data, recomputed for every node an update record touched:
 //   stat[n]  = CalculateAllocateScore + CalculateActualScore  (algorithm.go:70-87), wrapping u64
 //   narrow planes + the snapshot-wide "narrow eligible" verdict:
 //     every card field < 2^32-1, CardNumber < 2^32-1, stat < 2^24.
-// wide_flag[0] is set to 1 if any node with an SCV falls outside the narrow range,
+// wide_flag[0] counts the nodes with an SCV that fall outside the narrow range (META_WIDE marks them),
 // wide_flag[1] if a node's ordering key (see DevSnap::order) changed.
 #define NARROW_FIELD_LIMIT 0xFFFFFFFFull  /* exclusive */
 #define NARROW_STAT_LIMIT (1ull << 24)    /* exclusive */
-__global__ void k_prepare(DevSnap s, u32 *wide_flag) {
-    u32 n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= s.n_nodes) return;
+__device__ __forceinline__ void prepare_node(const DevSnap &s, u32 n, u32 *wide_flag) {
     const u32 meta = s.meta[n];
     bool wide = false;
     u64 st = 0;
@@ -80,7 +78,9 @@ __global__ void k_prepare(DevSnap s, u32 *wide_flag) {
 #pragma unroll
         for (int f = 0; f < NFIELD; ++f) s.n32[f][o] = (u32)s.f[f][o];
     }
-    if (wide) atomicOr(wide_flag, 1u);
+    // snapshot-wide verdict = number of wide nodes; this node's contribution changes by (now wide) - (was wide)
+    const bool was = (meta & META_WIDE) != 0;
+    if (wide != was) atomicAdd(wide_flag, wide ? 1u : 0xFFFFFFFFu);
     // cards worth visiting for the maxima, and the k-th largest FreeMemory of the healthy cards
     {
         const u32 nc = meta_ncards(meta), hm = meta_healthy(meta);
@@ -115,7 +115,7 @@ __global__ void k_prepare(DevSnap s, u32 *wide_flag) {
                     if (rank == (u32)k) tk[k] = (u32)v[F_FREE][b];
             }
         }
-        s.meta[n] = (meta & 0x00FFFFFFu) | (keep << 24);
+        s.meta[n] = (meta & 0x00FFFFFFu & ~META_WIDE) | (wide ? META_WIDE : 0u) | (keep << 24);
         uint4 *dst = reinterpret_cast<uint4 *>(s.tk32 + (size_t)n * G);
         dst[0] = make_uint4(tk[0], tk[1], tk[2], tk[3]);
         dst[1] = make_uint4(tk[4], tk[5], tk[6], tk[7]);
@@ -125,6 +125,12 @@ __global__ void k_prepare(DevSnap s, u32 *wide_flag) {
         s.order_key[n] = key;
         wide_flag[1] = 1u;
     }
+}
+
+// one thread per staged update record, right after k_scatter_updates: a commit costs what its updates cost
+__global__ void k_prepare_updates(DevSnap s, const UpdRec *__restrict__ upd, u32 n_upd, u32 *wide_flag) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_upd) prepare_node(s, upd[i].idx, wide_flag);
 }
 
 __global__ void k_iota(u32 *v, u32 n) {

@@ -1,6 +1,6 @@
 // fast_kernels.cuh -- the narrow (uint32) fast path.
 //
-// Applies when k_prepare found every card field and CardNumber < 2^32-1 and every static score
+// Applies when the derive step (prepare_node) found every card field and CardNumber < 2^32-1 and every static score
 // < 2^24 (any real cluster).  It produces bit-identical results to the direct kernels with far
 // fewer integer operations per (pod, node) pair:
 //

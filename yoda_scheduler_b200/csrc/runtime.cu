@@ -278,6 +278,12 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
     cudaMemsetAsync(s.stat, 0, (size_t)cap * 8, c->stream);
     cudaMemsetAsync(s.meta, 0, (size_t)cap * 4, c->stream);
     cudaMemsetAsync(s.order_key, 0xFF, (size_t)cap * 4, c->stream);  // no node has this key: the first commit orders
+    // derived planes of nodes no update ever touched: what the derive step would compute for "no SCV"
+    cudaMemsetAsync(s.stat32, 0, (size_t)cap * 4, c->stream);
+    cudaMemsetAsync(s.cardnum32, 0, (size_t)cap * 4, c->stream);
+    cudaMemsetAsync(s.tk32, 0, (size_t)cap * G * 4, c->stream);
+    for (int f = 0; f < NFIELD; ++f) cudaMemsetAsync(s.n32[f], 0, (size_t)cap * G * 4, c->stream);
+    cudaMemsetAsync(c->d_wide_flag, 0, 2 * sizeof(u32), c->stream);
     c->upd_cap = std::min<u32>(cfg->max_nodes, 1u << 16);
     if (cudaMallocHost((void **)&c->h_upd, (size_t)c->upd_cap * sizeof(UpdRec)) != cudaSuccess)
         return bail(fail(YODA_E_NOMEM, "cudaMallocHost of the update staging buffer failed"));
@@ -342,6 +348,8 @@ static int flush_updates(yoda_ctx *c) {
     CU(cudaMemcpyAsync(c->d_upd, c->h_upd, (size_t)c->n_upd * sizeof(UpdRec), cudaMemcpyHostToDevice, c->stream));
     const u32 threads = c->n_upd * G;
     k_scatter_updates<<<(threads + 255) / 256, 256, 0, c->stream>>>(c->snap, c->d_upd, c->n_upd);
+    CU(cudaGetLastError());
+    k_prepare_updates<<<(c->n_upd + 127) / 128, 128, 0, c->stream>>>(c->snap, c->d_upd, c->n_upd, c->d_wide_flag);  // derived data of the touched nodes
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(c->stream));  // the pinned buffer is reused right away
     for (u32 i = 0; i < c->n_upd; ++i) c->slot_of[c->h_upd[i].idx] = -1;
@@ -442,14 +450,12 @@ extern "C" int yoda_commit(yoda_ctx *c, uint64_t *epoch) {
     TRY(flush_updates(c));
     c->snap.n_nodes = c->n_nodes_pending;
     c->flushed_uncommitted = false;
-    CU(cudaMemsetAsync(c->d_wide_flag, 0, 2 * sizeof(u32), c->stream));
     const u32 N = c->snap.n_nodes;
-    if (N) {
-        k_prepare<<<(N + 255) / 256, 256, 0, c->stream>>>(c->snap, c->d_wide_flag);
-        CU(cudaGetLastError());
-    }
+    // the derived per-node data was brought up to date record by record (flush_updates); what is left is the
+    // snapshot-wide verdict: how many nodes are outside the narrow range, did any ordering key change
     u32 flag[2] = {0, 0};
     CU(cudaMemcpyAsync(flag, c->d_wide_flag, sizeof flag, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemsetAsync(c->d_wide_flag + 1, 0, sizeof(u32), c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->narrow_ok = (flag[0] == 0);
     if (N && (flag[1] || N != c->ord_nodes)) {  // metric ticks that leave the clocks alone keep the order
