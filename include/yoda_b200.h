@@ -154,6 +154,14 @@ int yoda_result_matrices(yoda_ctx *ctx, void **d_bits, void **d_raw, void **d_no
 /* element size of the raw matrix of the last YODA_EVAL_FULL result: 8 (int64), or 4 (uint32, YODA_EVAL_RAW32 honoured) */
 int yoda_result_raw_bytes(yoda_ctx *ctx, uint32_t *bytes);
 
+/* Introspection for tests and profiling (no counterpart in the reference).  After an evaluation that took the
+ * narrow table path: position k of the (group, memory)-sorted walk of the hot kernels -> index of that pod in the
+ * caller's batch, its requirement group and its class (any of the three arrays may be NULL; n = pods of that
+ * batch), and the pods per CTA the score pass and the output pass ran with.  The parity tests use it to aim at
+ * the pods on chunk / group / class boundaries.  YODA_E_STATE if the last evaluation took the exact kernels. */
+int yoda_debug_pod_order(yoda_ctx *ctx, uint32_t *orig, uint32_t *group, uint32_t *cls, uint32_t n, uint32_t *score_chunk,
+                         uint32_t *out_chunk);
+
 /* Yoda.NormalizeScore on an arbitrary score list, in place, on the device (scheduler.go:132-157):
  * used when the framework's list is not Yoda's own feasible set (other plugins filtered too). */
 int yoda_normalize_scores(yoda_ctx *ctx, int64_t *scores, uint32_t n);
@@ -180,7 +188,8 @@ int yoda_queue_order(yoda_ctx *ctx, const int64_t *priority, uint32_t n, uint32_
  * limits the list to YODA_NOALLOC_MAX_SCORES.  d_scores_in / d_scores_out are device pointers on
  * the current device (they may be equal); the work is queued on cuda_stream (cudaStream_t, NULL =
  * default stream) and is not waited for.  The first call on each device looks up the scratch
- * address; make that call before any stream capture begins.  Calls on one device share the
+ * address and makes the CUDA runtime load the module that holds it; make that call at start-up,
+ * before device memory runs short and before any stream capture begins.  Calls on one device share the
  * scratch: calls whose kernels overlap on the GPU race, so serialise them.  Longer lists are
  * rejected with YODA_E_RANGE. */
 #define YODA_NOALLOC_MAX_SCORES (1u << 20)

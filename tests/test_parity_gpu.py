@@ -546,3 +546,42 @@ def test_cluster_grows_and_cards_are_replaced():
     for k in got_m:
         assert np.array_equal(got_m[k], want_m[k]), k
     assert_matches_oracle(final, labels, got, got_m, what="grown cluster")
+
+
+def _hetero_nodes(rng, n):
+    """Nodes whose cards differ field by field and whose FreeMemory values collide across nodes (few distinct
+    values), so that lanes of one warp land on the same or on neighbouring pod positions in the maxima searches."""
+    nodes = []
+    for i in range(n):
+        nc = rng.choice([1, 2, 3, 8])
+        cards = [{"health": "Healthy" if rng.random() > 0.15 else "Unhealthy", "free": rng.choice([0, 100, 100, 2000, 2000, 7777, 16000, 40000]),
+                  "total": rng.choice([16000, 40536]), "clock": rng.choice([877, 1215, 1215, 5705]), "core": rng.randrange(1, 7000),
+                  "bandwidth": rng.randrange(0, 2000), "power": rng.randrange(1, 500)} for _ in range(nc)]
+        nodes.append({"name": f"n{i}", "has_scv": rng.random() > 0.05, "card_number": rng.choice([nc, 8, 0]), "cards": cards,
+                      "free_sum": sum(c["free"] for c in cards), "total_sum": sum(c["total"] for c in cards), "pods": []})
+    return nodes
+
+
+@pytest.mark.parametrize("n_nodes", [31, 33, 257])
+def test_maxima_lane_teaming_stress(n_nodes):
+    """k_max_thresholds lets whichever lanes of a warp arrive together at the same pod position share one atomic
+    (teams formed from __activemask() inside divergent code).  Nothing but results can catch a mis-teamed
+    reduction, so: tiny groups (1-3 pods, plus 9-12 pods to leave the small-batch path), heterogeneous nodes with
+    colliding FreeMemory values, 200 seeds per shape, every maximum against the oracle."""
+    with api.Context(n_nodes) as ctx:
+        for seed in range(200):
+            rng = random.Random(n_nodes * 1000 + seed)
+            snap = Snapshot.from_nodes(_hetero_nodes(rng, n_nodes))
+            ctx.load_snapshot(snap)
+            n_pods = rng.choice([1, 2, 3, 3, 9, 12])
+            labels = []
+            for _ in range(n_pods):
+                d = {"scv/memory": str(rng.choice([0, 1, 100, 101, 2000, 2001, 7777, 16000, 39999, 40001]))} if rng.random() < 0.8 else {}
+                if rng.random() < 0.4:
+                    d["scv/number"] = str(rng.choice([1, 2, 3]))
+                if rng.random() < 0.3:
+                    d["scv/clock"] = str(rng.choice([877, 1215, 5705]))
+                labels.append(d)
+            res = ctx.eval(pods_to_requests(labels), api.EVAL_DECIDE)
+            assert ctx.timing().path == 1
+            assert_matches_oracle(snap, labels, res, None, what=f"nodes={n_nodes} seed={seed}")

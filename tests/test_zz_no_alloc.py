@@ -27,6 +27,7 @@ def _noalloc(L, d_in, d_out, n, stream=None):
 
 def test_noalloc_matches_normalize_scores_twice_in_a_row():
     import torch
+    from oracle import oracle as ora
     from yoda_scheduler_b200 import _lib, api
 
     L = _lib.load()
@@ -44,6 +45,7 @@ def test_noalloc_matches_normalize_scores_twice_in_a_row():
             api.check(_noalloc(L, d_in.data_ptr(), d_out.data_ptr(), len(scores)))
             torch.cuda.synchronize()
             assert np.array_equal(d_out.cpu().numpy(), want)
+            assert d_out.cpu().numpy().tolist() == ora.normalize_score(scores.tolist())   # and the CPU oracle's
             # in place, on a caller-chosen stream
             st = torch.cuda.Stream(device=dev)
             st.wait_stream(torch.cuda.current_stream(dev))
@@ -57,6 +59,7 @@ def test_noalloc_matches_normalize_scores_twice_in_a_row():
             api.check(_noalloc(L, d.data_ptr(), d.data_ptr(), len(a)))
             torch.cuda.synchronize()
             assert np.array_equal(d.cpu().numpy(), ctx.normalize_scores(a))
+            assert d.cpu().numpy().tolist() == ora.normalize_score(list(scores))           # wrap cases included
 
 
 def test_noalloc_rejects_sizes_beyond_the_scratch():

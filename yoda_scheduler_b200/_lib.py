@@ -51,6 +51,7 @@ SYMBOLS = {
     "yoda_last_timing": (_I, [_P, C.POINTER(Timing)]),
     "yoda_result_matrices": (_I, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_U64)]),
     "yoda_result_raw_bytes": (_I, [_P, C.POINTER(_U32)]),
+    "yoda_debug_pod_order": (_I, [_P, _P, _P, _P, _U32, C.POINTER(_U32), C.POINTER(_U32)]),
     "yoda_normalize_scores": (_I, [_P, _P, _U32]),
     "yoda_eval_sequential": (_I, [_P, _P, _U32, _P, _P]),
     "yoda_queue_order": (_I, [_P, _P, _U32, _P]),

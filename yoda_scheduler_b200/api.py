@@ -128,6 +128,13 @@ class Context:
             "norm": np.stack([self.fetch_row(p, ROW_NORM, n) for p in range(n_pods)]) if n_pods else np.zeros((0, n), np.uint8),
         }
 
+    def pod_order(self, n_pods: int):
+        """(orig, group, cls, score_chunk, out_chunk) of the last table-path evaluation (yoda_debug_pod_order)."""
+        orig, grp, cls = (np.zeros(n_pods, np.uint32) for _ in range(3))
+        sc, oc = C.c_uint32(), C.c_uint32()
+        check(self.L.yoda_debug_pod_order(self.h, orig.ctypes.data, grp.ctypes.data, cls.ctypes.data, n_pods, C.byref(sc), C.byref(oc)))
+        return orig, grp, cls, sc.value, oc.value
+
     def normalize_scores(self, scores) -> np.ndarray:
         a = np.ascontiguousarray(scores, dtype=np.int64).copy()
         check(self.L.yoda_normalize_scores(self.h, a.ctypes.data, len(a)))

@@ -17,6 +17,11 @@
 // the GPU (different streams, or different host threads) corrupt each other's lowest/highest:
 // serialise them.  The array keeps whatever the previous call left in it; that is harmless because
 // a call reads back only the slots it has just written itself, so nothing has to be cleared.
+//
+// One caveat on "allocates nothing": the first call on a device makes the CUDA runtime load this
+// module there (code and the array itself are placed in device memory by the driver at that moment).
+// Make that first call at start-up -- before HBM fills up and before any stream capture -- and every
+// later call on that device touches no allocator at all.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -74,7 +79,8 @@ __global__ void __launch_bounds__(NA_THREADS) k_na_partials(const long long *__r
 }
 
 // second half: fold the n_blocks partial pairs, then rescale this block's slice (scheduler.go:147-153)
-__global__ void __launch_bounds__(NA_THREADS) k_na_apply(const long long *__restrict__ in, long long *out, uint32_t n,
+// `in` and `out` may be the same buffer (the header allows it), so neither is __restrict__
+__global__ void __launch_bounds__(NA_THREADS) k_na_apply(const long long *in, long long *out, uint32_t n,
                                                          const long long *partials, uint32_t n_blocks) {
     __shared__ long long s_lo[NA_THREADS / 32], s_hi[NA_THREADS / 32];
     long long lo = INT64_MAX, hi = 0;  // highest starts at 0 (scheduler.go:134); lowest at scores[0], i.e. the plain minimum

@@ -162,6 +162,7 @@ struct yoda_ctx {
     u32 *sq_stat = nullptr, *sq_pos = nullptr, *sq_order = nullptr, *sq_status = nullptr;
     u32 sq_pods_cap = 0;
     u32 score_slots = 0, out_slots = 0;  // CTAs of the hot kernels resident on the device at once
+    u32 last_score_chunk = 0, last_out_chunk = 0;  // pods per CTA the hot kernels of the last evaluation ran with (yoda_debug_pod_order)
     int n_sms = 0;  // DECIDE on one GPU: the score pass also yields counts and the node choice
 };
 
@@ -731,6 +732,7 @@ static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     if (p_end <= p_begin || !c->snap.n_nodes) return YODA_OK;
     const u32 tiles = (c->snap.n_nodes + HOT_WARPS * SCORE_NPL * 32 - 1) / (HOT_WARPS * SCORE_NPL * 32);
     const u32 chunk = hot_chunk(p_end - p_begin, tiles, c->score_slots, SCORE_CHUNK);
+    c->last_score_chunk = chunk;
     const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
     if (c->fw_decide_merged)
         k_fast_score<SCORE_NPL, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
@@ -747,6 +749,7 @@ static int fast_out_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     constexpr int NPL = 4;
     const u32 tiles = (c->snap.n_nodes + HOT_WARPS * NPL * 32 - 1) / (HOT_WARPS * NPL * 32);
     const u32 chunk = hot_chunk(p_end - p_begin, tiles, c->out_slots, HOT_CHUNK);
+    c->last_out_chunk = chunk;
     const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
     const bool full = (c->ph_flags & YODA_EVAL_FULL) != 0;
     if (full) c->res_raw32 = (c->ph_flags & YODA_EVAL_RAW32) != 0;
@@ -1175,6 +1178,26 @@ extern "C" int yoda_result_matrices(yoda_ctx *c, void **d_bits, void **d_raw, vo
     if (d_raw) *d_raw = c->d_raw;
     if (d_norm) *d_norm = c->d_norm;
     if (stride) *stride = c->stride;
+    return YODA_OK;
+}
+
+// Introspection: the order in which the table path walked the pods of the last evaluation.
+extern "C" int yoda_debug_pod_order(yoda_ctx *c, uint32_t *orig, uint32_t *group, uint32_t *cls, uint32_t n, uint32_t *score_chunk,
+                                    uint32_t *out_chunk) {
+    if (!c) return fail(YODA_E_ARG, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (c->ph_done != 3 || c->ph_path != 1 || n != c->ph_P) return fail(YODA_E_STATE, "the last evaluation did not take the table path with %u pods", n);
+    std::vector<PodS> tmp(n);
+    CU(cudaMemcpyAsync(tmp.data(), c->fw_pods, (size_t)n * sizeof(PodS), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    for (u32 i = 0; i < n; ++i) {
+        if (orig) orig[i] = tmp[i].orig;
+        if (group) group[i] = tmp[i].gid;
+        if (cls) cls[i] = tmp[i].cls;
+    }
+    if (score_chunk) *score_chunk = c->last_score_chunk;
+    if (out_chunk) *out_chunk = c->last_out_chunk;
     return YODA_OK;
 }
 
