@@ -1,7 +1,13 @@
 // Package yoda: the plugin surface kube-scheduler sees (name "yoda"; QueueSort, Filter,
 // PostFilter, Score, ScoreExtensions), with the per-(pod,node) arithmetic moved to the device.
-// The controller-runtime cache is still what watches Scv objects, but instead of being read on
-// every call it feeds the device-resident snapshot through event handlers.
+//
+// This file replaces pkg/yoda/scheduler.go of the reference checkout (see ../../apply_overlay.sh);
+// pkg/yoda/filter, collection, score and sort stay the reference's.  The controller-runtime cache
+// is still what watches Scv objects, but instead of being read (and deep-copied) on every call it
+// feeds the device-resident snapshot through event handlers.
+//
+// NOT COMPILED in the build image (no Go toolchain there); the same logic is tested through the
+// C ABI by the C++ mirror yoda_scheduler_b200/host/yoda_plugin.cpp.
 package yoda
 
 import (
@@ -39,33 +45,44 @@ var (
 	scheme = runtime.NewScheme()
 )
 
+// Yoda keeps the node-name <-> device-index dictionary and the host mirror of what the device
+// holds per node.  mu guards every field below it: informer goroutines write under Lock, the 16
+// framework goroutines of a cycle read under RLock.
 type Yoda struct {
 	handle framework.Handle
 	dev    *b200.Ctx
 
-	mu     sync.Mutex
-	index  map[string]uint32 // node name -> dense device index
-	names  []string
-	hasScv []bool
-	alloc  []uint64 // sum of StrToUint64(scv/memory) over the node's pods
-	dirty  bool
+	mu      sync.RWMutex
+	index   map[string]uint32 // node name -> dense device index
+	names   []string
+	hasScv  []bool
+	reject  []string // why the node's last Scv was refused by the device ("" = accepted)
+	alloc   []uint64 // sum of StrToUint64(scv/memory) over NodeInfo.Pods, as last sent to the device
+	gen     []int64  // NodeInfo.Generation the alloc sum was computed for
+	genSeen []bool
+	dirty   bool
 }
 
-// memo is what one cycle keeps in CycleState after its single device pass.
+// memo is what one cycle keeps in CycleState after its single device pass: a frozen view, so the
+// later Filter/Score/NormalizeScore calls of the cycle never look at state an informer may be changing.
 type memo struct {
-	res  b200.PodResult
-	n    uint32
-	bits []uint32
-	raw  []int64
-	norm []uint8
+	res    b200.PodResult
+	n      uint32   // nodes the evaluation covered; indices >= n were registered later
+	has    []bool   // copy of hasScv[:n] at evaluation time
+	reject []string // copy of reject[:n]
+	bits   []uint32
+	raw    []int64
+	norm   []uint8
 }
 
 func (m *memo) Clone() framework.StateData { return m }
+func (m *memo) known(i uint32) bool        { return i < m.n && m.has[i] }
 func (m *memo) feasible(i uint32) bool     { return i < m.n && (m.bits[i>>5]>>(i&31))&1 == 1 }
 
 func (y *Yoda) Name() string { return Name }
 
-// atoiOrZero is the label rule of the reference: strconv.Atoi, any error -> 0, then uint conversion.
+// atoiOrZero is the label rule of the reference (filter.go:60-74): strconv.Atoi, any error -> 0,
+// then the uint conversion.
 func atoiOrZero(s string) uint64 {
 	i, err := strconv.Atoi(s)
 	if err != nil {
@@ -82,6 +99,11 @@ func requirement(pod *v1.Pod) b200.PodReq {
 	return b200.MakeReq(hasNum, hasMem, hasClk, atoiOrZero(num), atoiOrZero(mem), atoiOrZero(clk))
 }
 
+// newYoda builds the plugin around an existing device context (New, and the bench harness).
+func newYoda(h framework.Handle, dev *b200.Ctx) *Yoda {
+	return &Yoda{handle: h, dev: dev, index: map[string]uint32{}}
+}
+
 func New(_ runtime.Object, h framework.Handle) (framework.Plugin, error) {
 	if err := scv.AddToScheme(scheme); err != nil {
 		return nil, err
@@ -90,7 +112,7 @@ func New(_ runtime.Object, h framework.Handle) (framework.Plugin, error) {
 	if err != nil {
 		return nil, err
 	}
-	y := &Yoda{handle: h, dev: dev, index: map[string]uint32{}}
+	y := newYoda(h, dev)
 
 	mgr, err := ctrl.NewManager(ctrl.GetConfigOrDie(), ctrl.Options{Scheme: scheme, MetricsBindAddress: "", LeaderElection: false, Port: 9443})
 	if err != nil {
@@ -104,20 +126,17 @@ func New(_ runtime.Object, h framework.Handle) (framework.Plugin, error) {
 		AddFunc:    func(o interface{}) { y.onScv(o.(*scv.Scv)) },
 		UpdateFunc: func(_, o interface{}) { y.onScv(o.(*scv.Scv)) },
 		DeleteFunc: func(o interface{}) {
+			if t, ok := o.(toolscache.DeletedFinalStateUnknown); ok { // tombstone of a missed delete
+				o = t.Obj
+			}
 			if s, ok := o.(*scv.Scv); ok {
 				y.onScvDelete(s.Name)
 			}
 		},
 	})
-	// running pods change CalculateAllocateScore: follow them through the scheduler's own pod informer
-	h.SharedInformerFactory().Core().V1().Pods().Informer().AddEventHandler(toolscache.ResourceEventHandlerFuncs{
-		AddFunc:    func(o interface{}) { y.onPod(o.(*v1.Pod), +1) },
-		DeleteFunc: func(o interface{}) {
-			if p, ok := o.(*v1.Pod); ok {
-				y.onPod(p, -1)
-			}
-		},
-	})
+	// CalculateAllocateScore reads NodeInfo.Pods of the scheduler's snapshot (algorithm.go:74-80), which
+	// holds assumed pods as well as bound ones.  No Pod informer can reproduce that, so the sums are taken
+	// from the very same snapshot at the start of each cycle (syncAllocLocked), node generation by generation.
 	go func() {
 		if err := mgr.Start(ctrl.SetupSignalHandler()); err != nil {
 			klog.Error(err)
@@ -127,7 +146,8 @@ func New(_ runtime.Object, h framework.Handle) (framework.Plugin, error) {
 	return y, nil
 }
 
-func (y *Yoda) indexOf(name string) uint32 {
+// indexOfLocked: callers hold mu for writing.
+func (y *Yoda) indexOfLocked(name string) uint32 {
 	if i, ok := y.index[name]; ok {
 		return i
 	}
@@ -135,49 +155,90 @@ func (y *Yoda) indexOf(name string) uint32 {
 	y.index[name] = i
 	y.names = append(y.names, name)
 	y.hasScv = append(y.hasScv, false)
+	y.reject = append(y.reject, "")
 	y.alloc = append(y.alloc, 0)
+	y.gen = append(y.gen, 0)
+	y.genSeen = append(y.genSeen, false)
 	return i
+}
+
+func (y *Yoda) lookup(name string) (uint32, bool) {
+	y.mu.RLock()
+	i, ok := y.index[name]
+	y.mu.RUnlock()
+	return i, ok
 }
 
 func (y *Yoda) onScv(s *scv.Scv) {
 	y.mu.Lock()
 	defer y.mu.Unlock()
-	i := y.indexOf(s.Name)
+	i := y.indexOfLocked(s.Name)
 	rec := b200.RecordFromScv(s) // healthy bit g = (CardList[g].Health == "Healthy")
 	if err := y.dev.Upsert(i, rec); err != nil {
+		// more than 8 cards, or TotalMemorySum == 0 (where the reference would panic, algorithm.go:71,86):
+		// the node must not keep answering from its previous record
 		klog.Errorf("Upsert SCV Error: %v", err)
+		_ = y.dev.Remove(i)
+		y.hasScv[i], y.reject[i], y.dirty = false, err.Error(), true
 		return
 	}
-	y.hasScv[i], y.dirty = true, true
+	y.hasScv[i], y.reject[i], y.dirty = true, "", true
 }
 
 func (y *Yoda) onScvDelete(name string) {
 	y.mu.Lock()
 	defer y.mu.Unlock()
-	i := y.indexOf(name)
+	i := y.indexOfLocked(name)
 	_ = y.dev.Remove(i)
-	y.hasScv[i], y.dirty = false, true
+	y.hasScv[i], y.reject[i], y.dirty = false, "", true
 }
 
-func (y *Yoda) onPod(p *v1.Pod, sign int) {
-	mem, ok := p.GetLabels()["scv/memory"]
-	if !ok || p.Spec.NodeName == "" {
+// syncAllocLocked brings the per-node allocateMemorySum in line with the scheduler's snapshot: the sum of
+// StrToUint64(scv/memory) over NodeInfo.Pods (algorithm.go:75-80).  Only nodes whose NodeInfo.Generation
+// moved since the last cycle are re-summed.  Callers hold mu for writing.
+func (y *Yoda) syncAllocLocked() {
+	if y.handle == nil {
 		return
 	}
-	y.mu.Lock()
-	defer y.mu.Unlock()
-	i := y.indexOf(p.Spec.NodeName)
-	if sign > 0 {
-		y.alloc[i] += atoiOrZero(mem)
-	} else {
-		y.alloc[i] -= atoiOrZero(mem)
+	infos, err := y.handle.SnapshotSharedLister().NodeInfos().List()
+	if err != nil {
+		klog.Errorf("List NodeInfos Error: %v", err)
+		return
 	}
-	_ = y.dev.SetAlloc(i, y.alloc[i])
-	y.dirty = true
+	for _, ni := range infos {
+		node := ni.Node()
+		if node == nil {
+			continue
+		}
+		i := y.indexOfLocked(node.Name)
+		if y.genSeen[i] && y.gen[i] == ni.Generation {
+			continue
+		}
+		var sum uint64
+		for _, pi := range ni.Pods {
+			if mem, ok := pi.Pod.GetLabels()["scv/memory"]; ok {
+				sum += atoiOrZero(mem)
+			}
+		}
+		y.gen[i], y.genSeen[i] = ni.Generation, true
+		if sum != y.alloc[i] {
+			y.alloc[i] = sum
+			if err := y.dev.SetAlloc(i, sum); err != nil {
+				klog.Errorf("SetAlloc Error: %v", err)
+			}
+			y.dirty = true
+		}
+	}
 }
 
 // cycle returns the memo of this scheduling cycle, evaluating the pod once on first use.
 func (y *Yoda) cycle(state *framework.CycleState, pod *v1.Pod) (*memo, error) {
+	state.RLock()
+	d, err := state.Read(memoKey)
+	state.RUnlock()
+	if err == nil {
+		return d.(*memo), nil
+	}
 	state.Lock()
 	defer state.Unlock()
 	if d, err := state.Read(memoKey); err == nil {
@@ -185,6 +246,7 @@ func (y *Yoda) cycle(state *framework.CycleState, pod *v1.Pod) (*memo, error) {
 	}
 	y.mu.Lock()
 	defer y.mu.Unlock()
+	y.syncAllocLocked()
 	if y.dirty {
 		if _, err := y.dev.Commit(); err != nil {
 			return nil, err
@@ -196,7 +258,12 @@ func (y *Yoda) cycle(state *framework.CycleState, pod *v1.Pod) (*memo, error) {
 		return nil, err
 	}
 	n := y.dev.NodeCount()
+	if int(n) > len(y.hasScv) {
+		n = uint32(len(y.hasScv))
+	}
 	m := &memo{res: res[0], n: n, bits: make([]uint32, (n+31)/32+1), raw: make([]int64, n+1), norm: make([]uint8, n+1)}
+	m.has = append([]bool(nil), y.hasScv[:n]...)
+	m.reject = append([]string(nil), y.reject[:n]...)
 	if n > 0 {
 		if err = y.dev.Row(0, b200.RowFeasible, unsafe.Pointer(&m.bits[0]), int((n+31)/32)*4); err == nil {
 			err = y.dev.Row(0, b200.RowRaw, unsafe.Pointer(&m.raw[0]), int(n)*8)
@@ -212,15 +279,21 @@ func (y *Yoda) cycle(state *framework.CycleState, pod *v1.Pod) (*memo, error) {
 	return m, nil
 }
 
+func notFound(name string) string { return "Scv.core.run-linux.com \"" + name + "\" not found" }
+
 func (y *Yoda) Filter(_ context.Context, state *framework.CycleState, pod *v1.Pod, node *framework.NodeInfo) *framework.Status {
 	name := node.Node().Name
 	m, err := y.cycle(state, pod)
 	if err != nil {
 		return framework.NewStatus(framework.Error, err.Error())
 	}
-	i, ok := y.index[name]
-	if !ok || !y.hasScv[i] {
-		return framework.NewStatus(framework.Unschedulable, "Node:"+name+" Scv.core.run-linux.com \""+name+"\" not found")
+	i, ok := y.lookup(name)
+	if !ok || !m.known(i) {
+		why := notFound(name)
+		if ok && i < m.n && m.reject[i] != "" {
+			why = "Scv rejected: " + m.reject[i]
+		}
+		return framework.NewStatus(framework.Unschedulable, "Node:"+name+" "+why)
 	}
 	if m.feasible(i) {
 		return framework.NewStatus(framework.Success, "")
@@ -250,16 +323,19 @@ func (y *Yoda) Score(_ context.Context, state *framework.CycleState, p *v1.Pod, 
 	if _, err := y.handle.SnapshotSharedLister().NodeInfos().Get(nodeName); err != nil {
 		return 0, framework.NewStatus(framework.Error, fmt.Sprintf("getting node %q from Snapshot: %v", nodeName, err))
 	}
-	i, ok := y.index[nodeName]
-	if !ok || !y.hasScv[i] {
-		return 0, framework.NewStatus(framework.Error, fmt.Sprintf("Score Node Error: Scv.core.run-linux.com %q not found", nodeName))
-	}
-	if _, err := state.Read("Max"); err != nil {
+	state.RLock()
+	_, err := state.Read("Max")
+	state.RUnlock()
+	if err != nil {
 		return 0, framework.NewStatus(framework.Error, fmt.Sprintf("Score Node Error: %v", err))
 	}
 	m, err := y.cycle(state, p)
 	if err != nil {
 		return 0, framework.NewStatus(framework.Error, fmt.Sprintf("Score Node Error: %v", err))
+	}
+	i, ok := y.lookup(nodeName)
+	if !ok || !m.known(i) { // also a node registered after this cycle's evaluation
+		return 0, framework.NewStatus(framework.Error, "Score Node Error: "+notFound(nodeName))
 	}
 	return m.raw[i], framework.NewStatus(framework.Success, "")
 }
@@ -267,19 +343,29 @@ func (y *Yoda) Score(_ context.Context, state *framework.CycleState, p *v1.Pod, 
 // NormalizeScore: when the list is Yoda's own feasible set with Yoda's scores the device already
 // normalized it; when other plugins removed nodes, rescale the given list on the device.
 func (y *Yoda) NormalizeScore(_ context.Context, state *framework.CycleState, _ *v1.Pod, scores framework.NodeScoreList) *framework.Status {
-	_ = scores[0] // an empty list panics, as upstream
+	_ = scores[0] // an empty list panics, as upstream (scheduler.go:135)
 	var m *memo
+	state.RLock()
 	if d, err := state.Read(memoKey); err == nil {
 		m = d.(*memo)
 	}
+	state.RUnlock()
 	own := m != nil && uint32(len(scores)) == b200.Feasible(&m.res)
-	for k := 0; own && k < len(scores); k++ {
-		i, ok := y.index[scores[k].Name]
-		own = ok && m.feasible(i) && m.raw[i] == scores[k].Score
+	idx := make([]uint32, len(scores))
+	if own {
+		y.mu.RLock()
+		for k := 0; own && k < len(scores); k++ {
+			i, ok := y.index[scores[k].Name]
+			// norm == 255 marks a rescale that wrapped outside [0,100]: the reference returns the wrapped int64,
+			// which only the exact list path below reproduces
+			own = ok && m.feasible(i) && m.raw[i] == scores[k].Score && m.norm[i] != 255
+			idx[k] = i
+		}
+		y.mu.RUnlock()
 	}
 	if own {
 		for k := range scores {
-			scores[k].Score = int64(m.norm[y.index[scores[k].Name]])
+			scores[k].Score = int64(m.norm[idx[k]])
 		}
 		return nil
 	}

@@ -585,3 +585,76 @@ def test_maxima_lane_teaming_stress(n_nodes):
             res = ctx.eval(pods_to_requests(labels), api.EVAL_DECIDE)
             assert ctx.timing().path == 1
             assert_matches_oracle(snap, labels, res, None, what=f"nodes={n_nodes} seed={seed}")
+
+
+def _mixed_snapshot(N, kinds, rng):
+    """A synthetic snapshot in which a few nodes carry a value outside the narrow (uint32) range."""
+    snap = synth.make_snapshot(N)
+    have = np.nonzero((snap.has_scv == 1) & (snap.n_cards > 0))[0]
+    picks = rng.choice(have, len(kinds), replace=False)
+    for n, kind in zip(picks, kinds):
+        if kind == "cardnum":      # Status.CardNumber is a Go uint: any 64-bit value is legal (filter.go:11-16)
+            snap.card_number[n] = np.uint64(1) << np.uint64(40)
+        elif kind == "stat":       # FreeMemorySum far above TotalMemorySum: the static score leaves 24 bits (algorithm.go:71)
+            snap.free_memory_sum[n] = np.uint64(1) << np.uint64(50)
+        elif kind == "stat_huge":  # ... and 63 bits: uint64 -> int64 turns the score into 0 (filter.go:84-86)
+            snap.free_memory_sum[n] = np.uint64(2**64 - 1) // np.uint64(100)
+            snap.total_memory_sum[n] = np.uint64(1)
+        elif kind == "power":      # a card field beyond 32 bits that is not a divisor of anyone else's score... but it is
+            snap.power[n, 0] = np.uint64(1) << np.uint64(33)   # a maximum: the classes of the pods it fits go wide
+        elif kind == "free":
+            snap.free_memory[n, 0] = np.uint64(1) << np.uint64(36)
+    return snap, picks
+
+
+@pytest.mark.parametrize("flags", [api.EVAL_FULL, api.EVAL_DECIDE])
+@pytest.mark.parametrize("kinds", [("cardnum",), ("stat",), ("stat_huge",), ("cardnum", "stat", "stat", "cardnum"), ("power",), ("free", "cardnum")])
+def test_mixed_wide_and_narrow_nodes(kinds, flags):
+    """One misreported SCV field must not cost the whole batch the table path: wide nodes are evaluated by the
+    exact kernels, every other node by the tables, in the same batch, and the result is the oracle's.  Wide card
+    fields that become a class maximum (power, free) still send the batch to the exact kernels as a whole."""
+    rng = np.random.default_rng(len(kinds) * 7 + flags)
+    N, P = 2100, 700
+    snap, picks = _mixed_snapshot(N, kinds, rng)
+    labels = synth.make_pod_labels(P, 19)
+    reqs = pods_to_requests(labels)
+    res, mats, t = gpu_cycle(snap, reqs, flags)
+    wide_maxima = any(k in ("power", "free") for k in kinds)
+    assert t.path == (0 if wide_maxima else 1), "wide nodes alone must not force the exact kernels on everyone"
+    o = assert_matches_oracle(snap, labels, res, mats, what=f"mixed {kinds}")
+    if "stat" in kinds and flags & api.EVAL_FULL:
+        # the wide node's score is the highest of every pod it fits: the 32-bit rescale cannot hold, the rows still match
+        assert (o["highest"] >= 2**32).any()
+    # small batches (their own code path) and RAW32 (a request the mixed snapshot cannot honour: int64 rows)
+    with api.Context(N) as ctx:
+        ctx.load_snapshot(snap)
+        r5 = ctx.eval(reqs[:5], flags)
+        assert np.array_equal(r5, res[:5])
+        if flags & api.EVAL_FULL:
+            m5 = ctx.fetch_all(5)
+            for k in m5:
+                assert np.array_equal(m5[k], mats[k][:5]), k
+            r32 = ctx.eval(reqs, flags | api.EVAL_RAW32)
+            assert ctx.result_raw_bytes() == 8 and np.array_equal(r32, res)
+            assert np.array_equal(ctx.fetch_row(3, api.ROW_RAW, N), mats["raw"][3])
+        # the node is repaired: the snapshot is narrow again and the wide list empties
+        fixed = synth.make_snapshot(N)
+        live = picks[fixed.has_scv[picks] == 1]
+        ctx.upsert_many(live, fixed.records(live))
+        ctx.commit()
+        again = ctx.eval(reqs, flags | api.EVAL_RAW32)
+        assert ctx.timing().path == 1
+        if flags & api.EVAL_FULL:
+            assert ctx.result_raw_bytes() == 4
+        want_fixed = ora.OracleCluster.from_snapshot(fixed).eval(labels, threads=8, full=False)
+        assert np.array_equal(again["chosen"], want_fixed["chosen"]) and np.array_equal(again["highest"], want_fixed["highest"])
+        assert np.array_equal(again["feasible"], want_fixed["count"])
+
+
+def test_mostly_wide_snapshot_goes_direct():
+    snap = synth.make_snapshot(600)
+    snap.card_number[:] = np.uint64(1) << np.uint64(40)
+    labels = synth.make_pod_labels(50, 3)
+    res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_FULL)
+    assert t.path == 0
+    assert_matches_oracle(snap, labels, res, mats)

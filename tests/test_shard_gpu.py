@@ -13,15 +13,24 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+@pytest.mark.parametrize("wide", [None, "stat", "cardnum"])
 @pytest.mark.parametrize("flags", [api.EVAL_FULL, api.EVAL_FULL | api.EVAL_FORCE_DIRECT, api.EVAL_DECIDE])
 @pytest.mark.parametrize("n_shards", [2, 3])
-def test_shards_on_one_gpu_equal_single(n_shards, flags):
+def test_shards_on_one_gpu_equal_single(n_shards, flags, wide):
     """All shards live on cuda:0 and run one after the other; the exchange between phases is an
-    element-wise max / sum over the shards' partial buffers (what NCCL does across GPUs)."""
+    element-wise max / sum over the shards' partial buffers (what NCCL does across GPUs).
+    wide: one node of the first shard has a static score beyond 2^32 ("stat": it becomes `highest` of most pods,
+    so the other, all-narrow shards must rescale their rows with 64-bit arithmetic) or a 40-bit CardNumber."""
     import torch
     dev = torch.device("cuda", 0)
     N, P = 3000, 500
     snap = synth.make_snapshot(N)
+    if wide:
+        node = int(np.nonzero((snap.has_scv == 1) & (snap.n_cards == 8) & (snap.card_number == 8))[0][3])
+        if wide == "stat":
+            snap.free_memory_sum[node] = np.uint64(1) << np.uint64(50)
+        else:
+            snap.card_number[node] = np.uint64(1) << np.uint64(40)
     reqs = synth.make_requests(P, 31)
     labels = synth.make_pod_labels(P, 31)
     with api.Context(N) as single:

@@ -23,6 +23,9 @@ typedef uint8_t u8;
 #define META_WIDE 0x20000u  // derived: the node (with an SCV) has a value outside the narrow range; counted in the snapshot-wide verdict
 // bits 24-31 (derived at commit): cards that no other card of the node dominates in all six fields -- the only ones
 // CollectMaxValues can ever take a maximum from
+// a node the narrow table path evaluates: it has an SCV and every value of it fits the narrow planes.  Wide nodes of a
+// mixed snapshot are left to the exact kernels (k_direct_pods over DevSnap-external wide list), in the same batch.
+__host__ __device__ __forceinline__ bool meta_table_node(u32 m) { return (m & (META_HAS_SCV | META_WIDE)) == META_HAS_SCV; }
 __host__ __device__ __forceinline__ u32 meta_keep(u32 m) { return m >> 24; }
 __host__ __device__ __forceinline__ u32 meta_healthy(u32 m) { return m & 0xFFu; }
 __host__ __device__ __forceinline__ u32 meta_ncards(u32 m) { return (m >> 8) & 0xFu; }

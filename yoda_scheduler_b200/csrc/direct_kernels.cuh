@@ -229,24 +229,60 @@ struct DirectTile {
     u64 cardnum[DTN];
     u64 stat[DTN];
     u32 meta[DTN];
+    u32 node[DTN];  // local node index of every tile slot
 };
 
-__device__ __forceinline__ void direct_load_tile(DirectTile &sm, const DevSnap &s, u32 n0, u32 n1) {
+// Stage nodes [n0, n1) -- positions in `node_list` when one is given (the snapshot's wide nodes, see below),
+// node indices otherwise -- into shared memory.
+__device__ __forceinline__ void direct_load_tile(DirectTile &sm, const DevSnap &s, const u32 *__restrict__ node_list, u32 n0, u32 n1) {
     const u32 cnt = (n1 - n0) * G;
+    if (node_list) {
 #pragma unroll
-    for (int f = 0; f < NFIELD; ++f)
-        for (u32 i = threadIdx.x; i < cnt; i += blockDim.x) sm.f[f][i] = s.f[f][(size_t)n0 * G + i];
+        for (int f = 0; f < NFIELD; ++f)
+            for (u32 i = threadIdx.x; i < cnt; i += blockDim.x) sm.f[f][i] = s.f[f][(size_t)node_list[n0 + i / G] * G + i % G];
+    } else {
+#pragma unroll
+        for (int f = 0; f < NFIELD; ++f)
+            for (u32 i = threadIdx.x; i < cnt; i += blockDim.x) sm.f[f][i] = s.f[f][(size_t)n0 * G + i];
+    }
     for (u32 i = threadIdx.x; i < n1 - n0; i += blockDim.x) {
-        sm.cardnum[i] = s.card_number[n0 + i];
-        sm.stat[i] = s.stat[n0 + i];
-        sm.meta[i] = s.meta[n0 + i];
+        const u32 n = node_list ? node_list[n0 + i] : n0 + i;
+        sm.cardnum[i] = s.card_number[n];
+        sm.stat[i] = s.stat[n];
+        sm.meta[i] = s.meta[n];
+        sm.node[i] = n;
     }
 }
 
+// lowest/highest as NormalizeScore uses them (scheduler.go:134-149), from the reduced partials
+__device__ __forceinline__ void dev_lo_hi(const u64 *hilo, u32 p, i64 &lo, i64 &hi) {
+    if (hilo[2 * (size_t)p + 1] == 0) {  // identity: no feasible node on any shard
+        lo = 0;
+        hi = 0;
+        return;
+    }
+    hi = (i64)hilo[2 * (size_t)p];
+    lo = (i64)(~hilo[2 * (size_t)p + 1]);
+    if (hi == lo) lo = (i64)((u64)lo - 1ull);
+}
+
+// Output side of the thread = pod kernel (MODE 2): where the verdicts and scores of the listed nodes go.
+struct DirectOut {
+    u64 *count, *ckey;
+    i64 *raw;    // FULL mode: result matrices (null otherwise); entries of the listed nodes are overwritten
+    u8 *norm;
+    u32 *bits;
+    u64 stride;
+    u32 packed;  // choice keys are (0xFFFFFFFF << 32 | ~global index): merged DECIDE after k_wide_promote
+};
+
 // MODE 0: collection.CollectMaxValues.  MODE 1: Score reduce (lowest/highest).
+// MODE 2: output pass (Score, NormalizeScore, feasible bit, count, node choice) for a LIST of nodes -- the wide
+// nodes of a mixed snapshot, a handful among many narrow ones, so thread = pod is the parallel axis there too.
+// node_list == nullptr: every node of the snapshot; otherwise only the n_list nodes it names.
 template <int MODE>
 __global__ void __launch_bounds__(DPT) k_direct_pods(DevSnap s, const PodC *__restrict__ pods, u32 P, u32 nodes_per_cta,
-                                                     u64 *max6, u64 *hilo) {
+                                                     u64 *max6, u64 *hilo, const u32 *__restrict__ node_list, u32 n_list, DirectOut out) {
     __shared__ DirectTile sm;
     const u32 p = blockIdx.x * DPT + threadIdx.x;
     const bool active = p < P;
@@ -255,21 +291,46 @@ __global__ void __launch_bounds__(DPT) k_direct_pods(DevSnap s, const PodC *__re
     u64 mx[6] = {1, 1, 1, 1, 1, 1};
     u64 hi = 0, nlo = 0;
     bool any = false;
-    if (MODE == 1 && active) {
+    i64 lo2 = 0, hi2 = 0;
+    u32 cnt = 0, best = 0xFFFFFFFFu;
+    if (MODE >= 1 && active) {
 #pragma unroll
         for (int i = 0; i < 6; ++i) mx[i] = max6[(size_t)p * 6 + i];
     }
+    if (MODE == 2 && active) dev_lo_hi(hilo, p, lo2, hi2);
+    const u32 n_total = node_list ? n_list : s.n_nodes;
     const u32 nbeg = blockIdx.y * nodes_per_cta;
-    const u32 nend = min(s.n_nodes, nbeg + nodes_per_cta);
+    const u32 nend = min(n_total, nbeg + nodes_per_cta);
     for (u32 n0 = nbeg; n0 < nend; n0 += DTN) {
         const u32 n1 = min(nend, n0 + DTN);
         __syncthreads();
-        direct_load_tile(sm, s, n0, n1);
+        direct_load_tile(sm, s, node_list, n0, n1);
         __syncthreads();
         if (!active) continue;
         for (u32 i = 0; i < n1 - n0; ++i) {
             u32 qual;
             const bool fit = direct_fit(pod, sm.meta[i], sm.cardnum[i], &sm.f[F_FREE][i * G], &sm.f[F_CLOCK][i * G], qual);
+            if (MODE == 2) {
+                u64 basic = 0;
+                if (fit)
+                    for (int g = 0; g < G; ++g)
+                        if ((qual >> g) & 1u)
+                            basic += direct_card_score(mx, sm.f[F_BW][i * G + g], sm.f[F_CLOCK][i * G + g], sm.f[F_CORE][i * G + g],
+                                                       sm.f[F_POWER][i * G + g], sm.f[F_FREE][i * G + g], sm.f[F_TOTAL][i * G + g]);
+                const i64 raw = (sm.meta[i] & META_HAS_SCV) ? dev_u64_to_i64(basic + sm.stat[i]) : 0;
+                const u32 n = sm.node[i];
+                if (fit) {
+                    cnt++;
+                    if (raw == hi2) best = min(best, n);
+                }
+                if (out.raw) {
+                    out.raw[(size_t)p * out.stride + n] = raw;
+                    out.norm[(size_t)p * out.stride + n] = fit ? dev_norm_u8(dev_norm_i64(raw, lo2, hi2)) : (u8)0;
+                    u32 *w = &out.bits[(size_t)p * (out.stride / 32) + (n >> 5)];
+                    if (fit) atomicOr(w, 1u << (n & 31)); else atomicAnd(w, ~(1u << (n & 31)));
+                }
+                continue;
+            }
             if (!fit) continue;
             if (MODE == 0) {
                 any = true;
@@ -302,24 +363,37 @@ __global__ void __launch_bounds__(DPT) k_direct_pods(DevSnap s, const PodC *__re
             for (int i = 0; i < 6; ++i)
                 if (mx[i] > 1) atomicMax(&max6[(size_t)p * 6 + i], mx[i]);
         }
-    } else {
+    } else if (MODE == 1) {
         if (nlo) {  // at least one feasible node seen
             atomicMax(&hilo[2 * (size_t)p], hi);
             atomicMax(&hilo[2 * (size_t)p + 1], nlo);
         }
+    } else {
+        if (cnt) atomicAdd(&out.count[p], (u64)cnt);
+        if (best != 0xFFFFFFFFu)
+            atomicMax(&out.ckey[p], out.packed ? (0xFFFFFFFF00000000ull | (u64)(0xFFFFFFFFu - (s.node_base + best))) : ckey_of(s.node_base + best));
     }
 }
 
-// lowest/highest as NormalizeScore uses them (scheduler.go:134-149), from the reduced partials
-__device__ __forceinline__ void dev_lo_hi(const u64 *hilo, u32 p, i64 &lo, i64 &hi) {
-    if (hilo[2 * (size_t)p + 1] == 0) {  // identity: no feasible node on any shard
-        lo = 0;
-        hi = 0;
-        return;
+// Merged DECIDE on a mixed snapshot: the score pass left, per pod, (best narrow score << 32 | ~index) in dkey.  Once
+// `highest` is final (the wide nodes' scores included), a narrow candidate stands only if its score is that
+// highest; it is re-keyed to (0xFFFFFFFF << 32 | ~index) so that the wide nodes' candidates (k_direct_pods<2>,
+// packed) compete with it on the index alone.
+__global__ void k_wide_promote(const u64 *__restrict__ hilo, const u64 *__restrict__ count, u64 *dkey, u32 P) {
+    const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const u64 k = dkey[p];
+    const bool stands = count[p] != 0 && (k >> 32) == hilo[2 * (size_t)p];
+    dkey[p] = stands ? (0xFFFFFFFF00000000ull | (k & 0xFFFFFFFFull)) : 0ull;
+}
+
+// the snapshot's wide nodes (META_WIDE), gathered at commit; order is irrelevant to every consumer
+__global__ void k_wide_list(const u32 *__restrict__ meta, u32 n_nodes, u32 *list, u32 *counter, u32 cap) {
+    const u32 n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n < n_nodes && (meta[n] & META_WIDE)) {
+        const u32 k = atomicAdd(counter, 1u);
+        if (k < cap) list[k] = n;
     }
-    hi = (i64)hilo[2 * (size_t)p];
-    lo = (i64)(~hilo[2 * (size_t)p + 1]);
-    if (hi == lo) lo = (i64)((u64)lo - 1ull);
 }
 
 // ------------------------------------------------------------------------------------------

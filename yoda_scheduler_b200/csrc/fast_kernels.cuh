@@ -19,6 +19,7 @@
 //     bits 24..27 of the same sum.
 #pragma once
 #include "common.cuh"
+#include "direct_kernels.cuh"  // dev_lo_hi / dev_norm_i64: the exact rescale of pods outside the 32-bit range
 
 // sorted pod record (32 B), broadcast to every lane of the hot kernels
 struct PodS {
@@ -220,7 +221,7 @@ __global__ void __launch_bounds__(MAXT) k_max_thresholds(DevSnap s, const GroupD
     const bool live = slot < s.n_nodes;
     const u32 nn = live ? s.order[slot] : 0;  // nodes with the same clock sit in the same warps
     const u32 meta = live ? s.meta[nn] : 0u;
-    const bool has = (meta & META_HAS_SCV) != 0;
+    const bool has = meta_table_node(meta);  // wide nodes: the exact kernels add their maxima afterwards
     const u32 hm = meta_healthy(meta), keep = meta_keep(meta);
     const u32 cardnum = s.cardnum32[nn];
     const u32 n_healthy = __popc(hm);
@@ -483,7 +484,16 @@ __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__r
     __syncthreads();
     const u32 n = blockIdx.x * CLST + threadIdx.x;
     if (n >= s.n_nodes) return;
-    const u32 hm = meta_healthy(s.meta[n]);
+    const u32 meta = s.meta[n];
+    if (meta & META_WIDE) {  // scored by the exact kernels; its narrow planes are truncations, keep them out of the tables
+        for (u32 k = 0; k < ncls; ++k) {
+            uint4 *dst = reinterpret_cast<uint4 *>(tables + ((size_t)(cid0 + k) * s.cap + n) * G);
+            dst[0] = make_uint4(0, 0, 0, 0);
+            dst[1] = make_uint4(0, 0, 0, 0);
+        }
+        return;
+    }
+    const u32 hm = meta_healthy(meta);
     // a node's eight values of one field are 32 contiguous bytes: two 16-byte loads per field; kept as 100x
     u32 a[6][G];
     bool node_plain = false;
@@ -562,7 +572,7 @@ __device__ __forceinline__ void hot_load_nodes(NodeRegs<NPL> &r, const DevSnap &
         load8(s.n32[F_FREE] + (size_t)nn * G, r.fr[j]);
         r.cardnum[j] = s.cardnum32[nn];
         r.stat[j] = in ? s.stat32[nn] : 0u;
-        r.ok[j] = in && (s.meta[nn] & META_HAS_SCV);
+        r.ok[j] = in && meta_table_node(s.meta[nn]);
         r.clkok[j] = true;
     }
 }
@@ -709,7 +719,7 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
         node[j] = in ? n : 0;
         cardnum[j] = s.cardnum32[node[j]];
         stat[j] = in ? s.stat32[node[j]] : 0u;
-        ok[j] = in && (s.meta[node[j]] & META_HAS_SCV);
+        ok[j] = in && meta_table_node(s.meta[node[j]]);
     }
     half_sync(bar_id);
     if (tid < SCORE_CHUNK / SCORE_BLK) {
@@ -837,11 +847,16 @@ struct OutSmem {
 __device__ __forceinline__ uint4 norm_consts(const u64 *__restrict__ hilo, u32 orig) {
     const u64 nlo = hilo[2 * (size_t)orig + 1];
     if (nlo == 0) return make_uint4(0, 0xFFFFFFFFu, 0, 0);  // no feasible node anywhere
-    const u32 hi = (u32)hilo[2 * (size_t)orig];
-    u32 lo = (u32)(~nlo);
+    const u64 hi64 = hilo[2 * (size_t)orig], lo64 = ~nlo;
+    // The 32-bit rescale below holds for lowest/highest of table nodes (scores < 2^25).  Wide nodes of a mixed snapshot,
+    // or another shard on the exact kernels, can push them beyond: such a pod is marked (z = 0, w = 1) and rescaled
+    // with plain 64-bit arithmetic.  y = the highest a table node can be compared with (none can reach one >= 2^32).
+    if (hi64 > 0xFFFFFFFEull || hi64 - lo64 > (1ull << 25)) return make_uint4((u32)lo64, hi64 > 0xFFFFFFFEull ? 0xFFFFFFFFu : (u32)hi64, 0, 1);
+    const u32 hi = (u32)hi64;
+    u32 lo = (u32)lo64;
     if (hi == lo) lo = lo - 1u;  // scheduler.go:147-149 (may become -1 = 0xFFFFFFFF)
     const u32 d = hi - lo;       // 1 .. 2^25
-    const u64 M = ((1ull << 57) / d) + 1ull;
+    const u64 M = ((1ull << 57) / d) + 1ull;  // >= 2^32: z is never 0 here
     return make_uint4(lo, hi, (u32)(M >> 32), (u32)M);
 }
 
@@ -878,7 +893,8 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
         const PodRegs pod = pod_from_smem(sm.sp, i);
         const uint4 pn = sm.sn[i];  // lo, hi, mhi, mlo
         const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
-        const bool nsame = same && (pn.x == cur_lo) && (pn.y == cur_hi);
+        const bool exact_norm = pn.z == 0 && pn.w == 1;  // lowest/highest outside the 32-bit rescale (see norm_consts)
+        const bool nsame = same && (pn.x == cur_lo) && (pn.y == cur_hi) && !exact_norm;
         const bool miss_any = !same || __any_sync(0xFFFFFFFFu, pod.m > bmin);
         if (miss_any) {
             if (pod.cls != cur_cls || pod.gid != cur_gid) hot_load_class(r, s, tables, pod.cls, pod.has_clock, pod.c, pod.reqC, base, lane);
@@ -922,7 +938,12 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
                 fitw[w] = word;
             }
         }
-        if (WRITE && !nsame) {
+        if (WRITE && exact_norm) {
+            i64 lo, hi;
+            dev_lo_hi(hilo, pod.orig, lo, hi);
+#pragma unroll 1
+            for (int j = 0; j < NPL; ++j) qn[j] = fitl[j] ? (u32)dev_norm_u8(dev_norm_i64((i64)raw64[j], lo, hi)) : 0u;
+        } else if (WRITE && !nsame) {
             // scheduler.go:152: (raw - lo) * 100 / (hi - lo), exact via the 57-bit reciprocal
 #pragma unroll
             for (int j = 0; j < NPL; ++j) {

@@ -101,7 +101,10 @@ struct yoda_ctx {
     void *ord_tmp = nullptr;
     size_t ord_tmp_bytes = 0;
     u32 ord_nodes = 0;           // node count the current DevSnap::order was built for
-    bool narrow_ok = false;
+    bool narrow_ok = false;  // no wide node at all
+    bool table_ok = false;   // few enough wide nodes for the table path (they go through the exact kernels, node by node)
+    u32 n_wide = 0;          // nodes outside the narrow range (META_WIDE)
+    u32 *d_wide_list = nullptr, *d_wide_cnt = nullptr;  // their local indices, gathered at commit
     uint64_t epoch = 0;
     // update staging
     UpdRec *h_upd = nullptr, *d_upd = nullptr;
@@ -311,6 +314,7 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     dev_free(s.cardnum32); dev_free(s.stat32); dev_free(s.tk32); dev_free(s.order); dev_free(s.order_key);
     dev_free(c->ord_keys_out); dev_free(c->ord_iota);
     if (c->ord_tmp) cudaFree(c->ord_tmp);
+    dev_free(c->d_wide_list); dev_free(c->d_wide_cnt);
     dev_free(c->d_wide_flag); dev_free(c->d_lohi); dev_free(c->d_list); dev_free(c->d_upd);
     dev_free(c->d_req); dev_free(c->d_pods); dev_free(c->d_max6); dev_free(c->d_count);
     dev_free(c->d_hilo); dev_free(c->d_ckey); dev_free(c->d_res);
@@ -458,7 +462,20 @@ extern "C" int yoda_commit(yoda_ctx *c, uint64_t *epoch) {
     CU(cudaMemcpyAsync(flag, c->d_wide_flag, sizeof flag, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemsetAsync(c->d_wide_flag + 1, 0, sizeof(u32), c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    c->narrow_ok = (flag[0] == 0);
+    c->n_wide = flag[0];
+    c->narrow_ok = (c->n_wide == 0);
+    // A few wide nodes (one misreported SCV field, a CardNumber beyond 32 bits) do not cost the batch the table path:
+    // the tables skip them and the exact kernels evaluate just those nodes.  Mostly-wide snapshots go direct wholesale.
+    c->table_ok = c->n_wide <= std::max(64u, N / 8);
+    if (c->n_wide && c->table_ok) {
+        if (!c->d_wide_list) {
+            TRY(dev_alloc(&c->d_wide_list, c->snap.cap));
+            TRY(dev_alloc(&c->d_wide_cnt, 1));
+        }
+        CU(cudaMemsetAsync(c->d_wide_cnt, 0, sizeof(u32), c->stream));
+        k_wide_list<<<(N + 255) / 256, 256, 0, c->stream>>>(c->snap.meta, N, c->d_wide_list, c->d_wide_cnt, c->snap.cap);
+        CU(cudaGetLastError());
+    }
     if (N && (flag[1] || N != c->ord_nodes)) {  // metric ticks that leave the clocks alone keep the order
         k_iota<<<(N + 255) / 256, 256, 0, c->stream>>>(c->ord_iota, N);
         CU(cudaGetLastError());
@@ -608,10 +625,45 @@ static int direct_pods_launch(yoda_ctx *c, int mode) {
     chunks = std::min(chunks, 65535u);
     const u32 npc = round_up((N + chunks - 1) / chunks, DTN);
     dim3 grid(gx, (N + npc - 1) / npc);
+    const DirectOut none{};
     if (mode == 0)
-        k_direct_pods<0><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo);
+        k_direct_pods<0><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo, nullptr, 0, none);
     else
-        k_direct_pods<1><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo);
+        k_direct_pods<1><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo, nullptr, 0, none);
+    LAUNCHED(c);
+    return YODA_OK;
+}
+
+// The wide nodes of a mixed snapshot, evaluated exactly while the table path takes all other nodes.
+// mode 0: their maxima, 1: their lowest/highest, 2: their part of the output pass.  thread = pod.
+static int wide_pods_launch(yoda_ctx *c, int mode) {
+    const u32 P = c->ph_P, W = c->n_wide;
+    if (!W || !c->snap.n_nodes) return YODA_OK;
+    const u32 gx = (P + DPT - 1) / DPT;
+    u32 chunks = std::max(1u, std::min((W + DTN - 1) / DTN, (592u + gx - 1) / gx));
+    chunks = std::min(chunks, 65535u);
+    const u32 npc = round_up((W + chunks - 1) / chunks, DTN);
+    dim3 grid(gx, (W + npc - 1) / npc);
+    DirectOut out{};
+    if (mode == 0) {
+        k_direct_pods<0><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo, c->d_wide_list, W, out);
+    } else if (mode == 1) {
+        k_direct_pods<1><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo, c->d_wide_list, W, out);
+    } else {
+        const bool full = (c->ph_flags & YODA_EVAL_FULL) != 0;
+        out.count = c->d_count;
+        out.ckey = c->d_ckey;
+        out.raw = full ? c->d_raw : nullptr;
+        out.norm = full ? c->d_norm : nullptr;
+        out.bits = full ? c->d_bits : nullptr;
+        out.stride = c->stride;
+        out.packed = c->fw_decide_merged ? 1u : 0u;
+        if (c->fw_decide_merged) {
+            k_wide_promote<<<(P + 255) / 256, 256, 0, c->stream>>>(c->d_hilo, c->d_count, c->d_ckey, P);
+            LAUNCHED(c);
+        }
+        k_direct_pods<2><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo, c->d_wide_list, W, out);
+    }
     LAUNCHED(c);
     return YODA_OK;
 }
@@ -752,7 +804,7 @@ static int fast_out_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     c->last_out_chunk = chunk;
     const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
     const bool full = (c->ph_flags & YODA_EVAL_FULL) != 0;
-    if (full) c->res_raw32 = (c->ph_flags & YODA_EVAL_RAW32) != 0;
+    if (full) c->res_raw32 = (c->ph_flags & YODA_EVAL_RAW32) != 0 && c->narrow_ok;  // a wide node's Score may not fit 32 bits
     if (full && c->res_raw32)
         k_fast_out<4, true, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
                                                                        c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride, chunk);
@@ -857,6 +909,7 @@ static int phase0(yoda_ctx *c, const yoda_pod_req *d_req) {
     k_init_partials<<<(P + 255) / 256, 256, 0, st>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, P);
     LAUNCHED(c);
     if (c->ph_path == 1) TRY(fast_phase0(c));
+    if (c->ph_path == 1) TRY(wide_pods_launch(c, 0));  // after k_max_scan, which stores the table nodes' maxima
     if (c->ph_path == 0) {
         CU(cudaEventRecord(c->ev[EV_PREP], st));
         TRY(direct_pods_launch(c, 0));
@@ -874,14 +927,17 @@ static int phase1(yoda_ctx *c) {
         // table path -- which a shard knows for itself only now.  One word, all-reduced with MAX: 1 = "I do not".
         cudaStream_t st = c->stream;
         CU(cudaMemsetAsync(c->d_agree, 0, sizeof(u64), st));
-        if (c->ph_path != 1) CU(cudaMemsetAsync(c->d_agree, 1, 1, st));  // little-endian: the word becomes 1
+        if (c->ph_path != 1 || c->n_wide) CU(cudaMemsetAsync(c->d_agree, 1, 1, st));  // little-endian: the word becomes 1
         NC(g_nccl.AllReduce(c->d_agree, c->d_agree, 1, ncclUint64, ncclMax, c->comm, st));
         CU(cudaMemcpyAsync(c->h_agree, c->d_agree, sizeof(u64), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
         c->fw_decide_merged = (*c->h_agree == 0);
     }
     if (c->ph_path == 0) c->fw_decide_merged = false;
-    if (c->ph_path == 1) TRY(fast_score_launch(c, 0, c->ph_P));
+    if (c->ph_path == 1) {
+        TRY(fast_score_launch(c, 0, c->ph_P));
+        TRY(wide_pods_launch(c, 1));
+    }
     if (c->ph_path == 0) TRY(direct_pods_launch(c, 1));
     CU(cudaEventRecord(c->ev[EV_SCORE], c->stream));
     return YODA_OK;
@@ -889,8 +945,11 @@ static int phase1(yoda_ctx *c) {
 
 // phase 2: output pass (matrices when FULL), feasible counts, node choice
 static int phase2(yoda_ctx *c) {
-    if (c->ph_path == 1 && c->fw_decide_merged) return YODA_OK;  // phase 1 already produced counts and choices
-    if (c->ph_path == 1) return fast_out_launch(c, 0, c->ph_P);
+    if (c->ph_path == 1 && c->fw_decide_merged) return wide_pods_launch(c, 2);  // phase 1 already produced the table nodes' counts and choices
+    if (c->ph_path == 1) {
+        TRY(fast_out_launch(c, 0, c->ph_P));
+        return wide_pods_launch(c, 2);  // overwrites the wide nodes' matrix entries
+    }
     return direct_out_launch(c);
 }
 
@@ -910,8 +969,8 @@ static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
     TRY(ensure_pods(c, P));
     c->stride = round_up(std::max(c->snap.n_nodes, 1u), 1024);  // rows padded to the hot kernels' CTA tile
     if (flags & ~(YODA_EVAL_FULL | YODA_EVAL_FORCE_DIRECT | YODA_EVAL_RAW32)) return fail(YODA_E_ARG, "unknown evaluation flags 0x%x", flags);
-    c->ph_path = (c->narrow_ok && !(flags & YODA_EVAL_FORCE_DIRECT)) ? 1 : 0;
-    if (flags & YODA_EVAL_FULL) TRY(ensure_matrices(c, P, c->stride, (c->ph_path == 1 && (flags & YODA_EVAL_RAW32)) ? 4u : 8u));
+    c->ph_path = (c->table_ok && !(flags & YODA_EVAL_FORCE_DIRECT)) ? 1 : 0;
+    if (flags & YODA_EVAL_FULL) TRY(ensure_matrices(c, P, c->stride, (c->ph_path == 1 && c->narrow_ok && (flags & YODA_EVAL_RAW32)) ? 4u : 8u));
     if (c->ph_path == 1) TRY(ensure_fast(c, P));
     c->ph_P = P;
     c->ph_flags = flags;
@@ -1055,7 +1114,7 @@ extern "C" int yoda_eval_sequential(yoda_ctx *c, const yoda_pod_req *pods, u32 P
     if (P == 0) return YODA_OK;
     if (c->comm) return fail(YODA_E_STATE, "sequential-commit evaluation is not available on a node-sharded context");
     TRY(begin_locked(c, P, YODA_EVAL_DECIDE));
-    if (c->ph_path != 1)
+    if (c->ph_path != 1 || !c->narrow_ok)
         return fail(YODA_E_RANGE, "sequential-commit evaluation needs a narrow snapshot (card fields < 2^32-1, static scores < 2^24)");
     cudaStream_t st = c->stream;
     if (!c->sq_alloc) {
