@@ -2,9 +2,11 @@
 // every buffer is passed for the duration of one call only.
 package b200
 
+// Search paths come from the environment, because this package lives inside a copy of the reference tree
+// (see go/apply_overlay.sh): CGO_CFLAGS=-I<repo>/include CGO_LDFLAGS="-L<repo>/yoda_scheduler_b200 -Wl,-rpath,...".
+
 /*
-#cgo CFLAGS: -I${SRCDIR}/../../../../include
-#cgo LDFLAGS: -L${SRCDIR}/../../../../yoda_scheduler_b200 -lyoda_b200
+#cgo LDFLAGS: -lyoda_b200
 #include <stdlib.h>
 #include "yoda_b200.h"
 */
@@ -12,6 +14,7 @@ import "C"
 
 import (
 	"fmt"
+	"runtime"
 	"unsafe"
 )
 
@@ -33,15 +36,23 @@ type (
 
 type Ctx struct{ h *C.yoda_ctx }
 
-func lastErr(rc C.int) error {
-	return fmt.Errorf("yoda_b200 error %d: %s", int(rc), C.GoString(C.yoda_last_error()))
+// call runs one C entry point and, if it failed, fetches its message.  yoda_last_error() is thread-local on
+// the C side and a goroutine may be moved to another OS thread between two cgo calls, so the pair is made
+// on a locked thread: the message read is the one the failing call wrote.
+func call(f func() C.int) error {
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
+	if rc := f(); rc != 0 {
+		return fmt.Errorf("yoda_b200 error %d: %s", int(rc), C.GoString(C.yoda_last_error()))
+	}
+	return nil
 }
 
 func New(device int, maxNodes uint32) (*Ctx, error) {
 	cfg := C.yoda_config{device: C.int32_t(device), max_nodes: C.uint32_t(maxNodes), shard_count: 1}
 	var h *C.yoda_ctx
-	if rc := C.yoda_create(&cfg, &h); rc != 0 {
-		return nil, lastErr(rc)
+	if err := call(func() C.int { return C.yoda_create(&cfg, &h) }); err != nil {
+		return nil, err
 	}
 	return &Ctx{h}, nil
 }
@@ -49,30 +60,21 @@ func New(device int, maxNodes uint32) (*Ctx, error) {
 func (c *Ctx) Close() { C.yoda_destroy(c.h); c.h = nil }
 
 func (c *Ctx) Upsert(idx uint32, rec *NodeRecord) error {
-	if rc := C.yoda_node_upsert(c.h, C.uint32_t(idx), rec); rc != 0 {
-		return lastErr(rc)
-	}
-	return nil
+	return call(func() C.int { return C.yoda_node_upsert(c.h, C.uint32_t(idx), rec) })
 }
 
 func (c *Ctx) SetAlloc(idx uint32, sum uint64) error {
-	if rc := C.yoda_node_set_alloc(c.h, C.uint32_t(idx), C.uint64_t(sum)); rc != 0 {
-		return lastErr(rc)
-	}
-	return nil
+	return call(func() C.int { return C.yoda_node_set_alloc(c.h, C.uint32_t(idx), C.uint64_t(sum)) })
 }
 
 func (c *Ctx) Remove(idx uint32) error {
-	if rc := C.yoda_node_remove(c.h, C.uint32_t(idx)); rc != 0 {
-		return lastErr(rc)
-	}
-	return nil
+	return call(func() C.int { return C.yoda_node_remove(c.h, C.uint32_t(idx)) })
 }
 
 func (c *Ctx) Commit() (uint64, error) {
 	var e C.uint64_t
-	if rc := C.yoda_commit(c.h, &e); rc != 0 {
-		return 0, lastErr(rc)
+	if err := call(func() C.int { return C.yoda_commit(c.h, &e) }); err != nil {
+		return 0, err
 	}
 	return uint64(e), nil
 }
@@ -94,29 +96,26 @@ func (c *Ctx) Eval(pods []PodReq, full bool) ([]PodResult, error) {
 		// rows are only ever read through yoda_fetch_row (int64 either way): let the device keep the scores as uint32
 		flags = C.uint32_t(C.YODA_EVAL_FULL | C.YODA_EVAL_RAW32)
 	}
-	rc := C.yoda_eval_batch(c.h, (*C.yoda_pod_req)(unsafe.Pointer(&pods[0])), C.uint32_t(len(pods)), flags,
-		(*C.yoda_pod_result)(unsafe.Pointer(&out[0])))
-	if rc != 0 {
-		return nil, lastErr(rc)
+	err := call(func() C.int {
+		return C.yoda_eval_batch(c.h, (*C.yoda_pod_req)(unsafe.Pointer(&pods[0])), C.uint32_t(len(pods)), flags,
+			(*C.yoda_pod_result)(unsafe.Pointer(&out[0])))
+	})
+	if err != nil {
+		return nil, err
 	}
 	return out, nil
 }
 
 func (c *Ctx) Row(pod uint32, kind int, dst unsafe.Pointer, bytes int) error {
-	if rc := C.yoda_fetch_row(c.h, C.uint32_t(pod), C.int(kind), dst, C.size_t(bytes)); rc != 0 {
-		return lastErr(rc)
-	}
-	return nil
+	return call(func() C.int { return C.yoda_fetch_row(c.h, C.uint32_t(pod), C.int(kind), dst, C.size_t(bytes)) })
 }
 
 // NormalizeScores: scheduler.go:132-157 on an arbitrary list, in place, on the device.
 func (c *Ctx) NormalizeScores(scores []int64) error {
-	if rc := C.yoda_normalize_scores(c.h, (*C.int64_t)(unsafe.Pointer(&scores[0])), C.uint32_t(len(scores))); rc != 0 {
-		return lastErr(rc)
-	}
-	return nil
+	return call(func() C.int {
+		return C.yoda_normalize_scores(c.h, (*C.int64_t)(unsafe.Pointer(&scores[0])), C.uint32_t(len(scores)))
+	})
 }
-
 
 // QueueOrder: batch order under sort.Less (scv/priority, higher first, stable).
 func (c *Ctx) QueueOrder(priority []int64) ([]uint32, error) {
@@ -124,9 +123,11 @@ func (c *Ctx) QueueOrder(priority []int64) ([]uint32, error) {
 	if len(priority) == 0 {
 		return order, nil
 	}
-	rc := C.yoda_queue_order(c.h, (*C.int64_t)(unsafe.Pointer(&priority[0])), C.uint32_t(len(priority)), (*C.uint32_t)(unsafe.Pointer(&order[0])))
-	if rc != 0 {
-		return nil, lastErr(rc)
+	err := call(func() C.int {
+		return C.yoda_queue_order(c.h, (*C.int64_t)(unsafe.Pointer(&priority[0])), C.uint32_t(len(priority)), (*C.uint32_t)(unsafe.Pointer(&order[0])))
+	})
+	if err != nil {
+		return nil, err
 	}
 	return order, nil
 }
@@ -141,9 +142,11 @@ func (c *Ctx) EvalSequential(pods []PodReq, order []uint32) ([]PodResult, error)
 	if order != nil {
 		op = (*C.uint32_t)(unsafe.Pointer(&order[0]))
 	}
-	rc := C.yoda_eval_sequential(c.h, (*C.yoda_pod_req)(unsafe.Pointer(&pods[0])), C.uint32_t(len(pods)), op, (*C.yoda_pod_result)(unsafe.Pointer(&out[0])))
-	if rc != 0 {
-		return nil, lastErr(rc)
+	err := call(func() C.int {
+		return C.yoda_eval_sequential(c.h, (*C.yoda_pod_req)(unsafe.Pointer(&pods[0])), C.uint32_t(len(pods)), op, (*C.yoda_pod_result)(unsafe.Pointer(&out[0])))
+	})
+	if err != nil {
+		return nil, err
 	}
 	return out, nil
 }

@@ -843,6 +843,9 @@ struct OutSmem {
     u32 best_s[HOT_WARPS][HOT_CHUNK];
 };
 
+// the rare exact rescale, kept out of line so that its 64-bit division does not bloat the hot loop
+__device__ __noinline__ u32 exact_norm_u8(u32 raw, i64 lo, i64 hi) { return (u32)dev_norm_u8(dev_norm_i64((i64)raw, lo, hi)); }
+
 // rescale constants of one pod from the (cross-shard reduced) lowest/highest: norm = ((raw-lo)*100*M) >> 57
 __device__ __forceinline__ uint4 norm_consts(const u64 *__restrict__ hilo, u32 orig) {
     const u64 nlo = hilo[2 * (size_t)orig + 1];
@@ -941,8 +944,8 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
         if (WRITE && exact_norm) {
             i64 lo, hi;
             dev_lo_hi(hilo, pod.orig, lo, hi);
-#pragma unroll 1
-            for (int j = 0; j < NPL; ++j) qn[j] = fitl[j] ? (u32)dev_norm_u8(dev_norm_i64((i64)raw64[j], lo, hi)) : 0u;
+#pragma unroll  // (constant indices: a rolled loop would move qn/fitl/raw64 to local memory for every pod)
+            for (int j = 0; j < NPL; ++j) qn[j] = exact_norm_u8((u32)raw64[j], lo, hi) & fitl[j];
         } else if (WRITE && !nsame) {
             // scheduler.go:152: (raw - lo) * 100 / (hi - lo), exact via the 57-bit reciprocal
 #pragma unroll
