@@ -323,19 +323,19 @@ func (y *Yoda) Score(_ context.Context, state *framework.CycleState, p *v1.Pod, 
 	if _, err := y.handle.SnapshotSharedLister().NodeInfos().Get(nodeName); err != nil {
 		return 0, framework.NewStatus(framework.Error, fmt.Sprintf("getting node %q from Snapshot: %v", nodeName, err))
 	}
-	state.RLock()
-	_, err := state.Read("Max")
-	state.RUnlock()
-	if err != nil {
-		return 0, framework.NewStatus(framework.Error, fmt.Sprintf("Score Node Error: %v", err))
-	}
 	m, err := y.cycle(state, p)
 	if err != nil {
 		return 0, framework.NewStatus(framework.Error, fmt.Sprintf("Score Node Error: %v", err))
 	}
 	i, ok := y.lookup(nodeName)
-	if !ok || !m.known(i) { // also a node registered after this cycle's evaluation
+	if !ok || !m.known(i) { // scheduler.go:117-122; also a node registered after this cycle's evaluation
 		return 0, framework.NewStatus(framework.Error, "Score Node Error: "+notFound(nodeName))
+	}
+	state.RLock()
+	_, err = state.Read("Max") // algorithm.go:29-33
+	state.RUnlock()
+	if err != nil {
+		return 0, framework.NewStatus(framework.Error, fmt.Sprintf("Score Node Error: %v", err))
 	}
 	return m.raw[i], framework.NewStatus(framework.Success, "")
 }

@@ -147,6 +147,9 @@ int yoda_eval_batch_device(yoda_ctx *ctx, const void *d_pods, uint32_t n_pods, u
 /* copy one row of the last YODA_EVAL_FULL result to the host: the O(1)-per-node memo behind
  * later Filter/Score/NormalizeScore calls of the same cycle */
 int yoda_fetch_row(yoda_ctx *ctx, uint32_t pod, int kind, void *dst, size_t bytes);
+/* the three rows of one pod in one call (three DMA copies through pinned staging, one synchronisation): what the
+ * plugin memoises at the first Filter of a cycle.  bits: (n_nodes+31)/32 words, raw: n_nodes int64, norm: n_nodes bytes */
+int yoda_fetch_rows(yoda_ctx *ctx, uint32_t pod, uint32_t n_nodes, uint32_t *bits, int64_t *raw, uint8_t *norm);
 int yoda_sync(yoda_ctx *ctx);
 int yoda_last_timing(yoda_ctx *ctx, yoda_timing *t);
 /* device pointers of the last YODA_EVAL_FULL matrices (for zero-copy consumers); row strides in elements */

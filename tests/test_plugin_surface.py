@@ -158,3 +158,30 @@ def test_informer_events_change_the_next_cycle(plug):
     assert y.filter(st, pod, h.node_infos["B"]).code == pl.UNSCHEDULABLE
     y.on_scv_upsert("B", _status_of(nodes[1]))
     assert raw_of("B") == before
+
+
+def test_node_registered_mid_cycle_and_refused_scv(plug):
+    """A node whose Scv arrives between Filter and Score of a cycle is not part of that cycle's evaluation: Score
+    answers "not found" instead of indexing past the memo.  An Scv the device refuses (TotalMemorySum == 0, where
+    the reference would panic) takes the node's previous record out of service."""
+    pl, y, h, nodes = plug
+    from yoda_scheduler_b200 import api
+    pod, st = pl.Pod(labels={}), pl.CycleState()
+    for n in nodes:
+        y.filter(st, pod, h.node_infos[n["name"]])
+    y.post_filter(st, pod)
+    h.node_infos["late"] = pl.NodeInfo("late")
+    y.on_scv_upsert("late", _status_of(nodes[0]))
+    v, s = y.score(st, pod, "late")
+    assert (v, s.code) == (0, pl.ERROR) and "not found" in s.message
+    assert y.filter(st, pod, h.node_infos["late"]).code == pl.UNSCHEDULABLE
+    st2 = pl.CycleState()                                  # the next cycle sees it
+    assert y.filter(st2, pod, h.node_infos["late"]).is_success()
+    broken = _status_of(nodes[0])
+    broken["TotalMemorySum"] = 0
+    with pytest.raises(api.YodaError):
+        y.on_scv_upsert("A", broken)
+    st3 = pl.CycleState()
+    assert y.filter(st3, pod, h.node_infos["A"]).code == pl.UNSCHEDULABLE
+    y.on_scv_upsert("A", _status_of(nodes[0]))
+    assert y.filter(pl.CycleState(), pod, h.node_infos["A"]).is_success()

@@ -6,7 +6,8 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SO = os.path.join(HERE, "libyoda_b200.so")
+# YODA_B200_SO: load another build of the library instead (kernel-tuning experiments: variants compiled by hand with -D flags)
+SO = os.environ.get("YODA_B200_SO") or os.path.join(HERE, "libyoda_b200.so")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-shared",
@@ -18,6 +19,8 @@ def sources():
 
 
 def stale() -> bool:
+    if os.environ.get("YODA_B200_SO"):
+        return False  # a hand-built variant: never rebuilt behind the experimenter's back
     if not os.path.exists(SO):
         return True
     t = os.path.getmtime(SO)

@@ -47,6 +47,7 @@ SYMBOLS = {
     "yoda_eval_batch": (_I, [_P, _P, _U32, _U32, _P]),
     "yoda_eval_batch_device": (_I, [_P, _P, _U32, _U32, _P]),
     "yoda_fetch_row": (_I, [_P, _U32, _I, _P, C.c_size_t]),
+    "yoda_fetch_rows": (_I, [_P, _U32, _U32, _P, _P, _P]),
     "yoda_sync": (_I, [_P]),
     "yoda_last_timing": (_I, [_P, C.POINTER(Timing)]),
     "yoda_result_matrices": (_I, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_U64)]),

@@ -683,10 +683,11 @@ __device__ __forceinline__ PodRegs pod_from_smem(const uint4 *sp, u32 i) {
 // dropped: both passes need ~128 registers per thread, so they only time-share the SM).
 __device__ __forceinline__ void half_sync(int bar_id) { asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(HOT_THREADS) : "memory"); }
 
-#define SCORE_BLK 4
+#define SCORE_BLK 4  // chunk sizes stay multiples of this (hot_chunk in runtime.cu)
 struct ScoreSmem {
     uint4 sp[SCORE_CHUNK * 2];
-    uint4 blk[SCORE_CHUNK / SCORE_BLK];  // gid (or ~0 if mixed), cls, first m, last m of four consecutive pods
+    u32 m_s[SCORE_CHUNK];    // memory value of every pod of the chunk (ascending inside a run)
+    u32 key_s[SCORE_CHUNK];  // run key: requirement group << 12 | class; a (group, class) run is contiguous in the sorted order
     __align__(16) u32 hi_s[HOT_WARPS][SCORE_CHUNK];
     __align__(16) u32 lo_s[HOT_WARPS][SCORE_CHUNK];
     __align__(16) u32 cnt_s[HOT_WARPS][SCORE_CHUNK];   // DECIDE only: feasible nodes of the warp's slots
@@ -695,9 +696,12 @@ struct ScoreSmem {
 };
 
 // score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145).
-// Pods are taken four at a time: a per-chunk summary says whether the four share group and class
-// with ascending memory values; if so and no lane's validity bound is crossed by the largest of
-// the four, all four inherit the warp's current (highest, lowest) with one test.
+// A warp does not walk the pods one by one.  After it has evaluated its nodes for pod i, everything it knows
+// stays valid up to the first later pod that either starts another (group, class) run or asks for more memory than
+// the smallest validity bound among its nodes -- and because the memory values ascend inside a run, that pod is
+// found by a warp-wide look-ahead over the staged values, 32 pods per step (one compare + vote), instead of a
+// test per pod.  The warp's (highest, lowest) are stored only at the pods it stopped at, under mark bits; the pods
+// in between inherit the entry of the last marked pod before them.
 // DECIDE (per-pod results only, one GPU): the same pass also counts the feasible nodes and tracks the
 // lowest-index node holding the top score, packed as (score << 32 | ~index) so that one 64-bit
 // atomicMax across the node tiles yields the choice -- no output pass is needed at all.
@@ -709,6 +713,12 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
     const u32 c0 = p_begin + chunk * chunk_pods;
     const u32 cn = min(chunk_pods, p_end - c0);
     for (u32 i = tid; i < cn * 2; i += HOT_THREADS) sm.sp[i] = reinterpret_cast<const uint4 *>(pods + c0)[i];
+    for (u32 i = tid; i < cn; i += HOT_THREADS) {
+        const PodS &ps = pods[c0 + i];
+        sm.m_s[i] = ps.m;
+        sm.key_s[i] = (ps.gid << FAST_GID_BITS) | ps.cls;  // classes are capped at 4096 (FAST_CLASS_CAP)
+    }
+    if (tid < HOT_WARPS * (SCORE_CHUNK / 32)) (&sm.mark_s[0][0])[tid] = 0u;
     const u32 base = (tile * HOT_WARPS + warp) * (NPL * 32);
     u32 node[NPL], cardnum[NPL], stat[NPL];
     bool ok[NPL];
@@ -722,89 +732,65 @@ __device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u
         ok[j] = in && meta_table_node(s.meta[node[j]]);
     }
     half_sync(bar_id);
-    if (tid < SCORE_CHUNK / SCORE_BLK) {
-        const u32 b0 = tid * SCORE_BLK;
-        uint4 v = make_uint4(0xFFFFFFFFu, 0, 0, 0);
-        if (b0 + SCORE_BLK <= cn) {
-            const uint4 a0 = sm.sp[2 * b0], c1 = sm.sp[2 * b0 + 1];
-            bool okb = true;
-            u32 prev = a0.x;
-#pragma unroll
-            for (int k = 1; k < SCORE_BLK; ++k) {
-                const uint4 a = sm.sp[2 * (b0 + k)], c = sm.sp[2 * (b0 + k) + 1];
-                okb = okb && c.z == c1.z && c.x == c1.x && a.x >= prev;
-                prev = a.x;
-            }
-            if (okb) v = make_uint4(c1.z, c1.x, a0.x, prev);
-        }
-        sm.blk[tid] = v;
-    }
-    half_sync(bar_id);
-    u32 cur_cls = 0xFFFFFFFFu, cur_gid = 0xFFFFFFFEu, cur_m = 0;
+    u32 cur_key = 0xFFFFFFFFu;
     u32 hi_l[NPL], lo_l[NPL], bound[NPL];
 #pragma unroll
     for (int j = 0; j < NPL; ++j) { hi_l[j] = 0; lo_l[j] = 0xFFFFFFFFu; bound[j] = 0; }
-    u32 bmin = 0;  // min over the lane's slots of bound[j]
-    // A warp's (highest, lowest) only changes when one of its slots is re-evaluated, so it is stored for those
-    // pods alone, with a mark bit; a pod without a mark takes the entry of the last marked pod before it.  The
-    // cache-hit path therefore writes nothing at all.  Marks are kept per window of 32 pods.
-    for (u32 w0 = 0; w0 < SCORE_CHUNK; w0 += 32) {
-        u32 mk = 0;
-        const u32 w1 = min(cn, w0 + 32);
-        for (u32 i0 = w0; i0 < w1; i0 += SCORE_BLK) {
-            const uint4 bs = sm.blk[i0 / SCORE_BLK];
-            if (bs.x == cur_gid && bs.y == cur_cls && bs.z >= cur_m && !__any_sync(0xFFFFFFFFu, bs.w > bmin)) {
-                cur_m = bs.w;
-                continue;
-            }
-            const u32 i1 = min(cn, i0 + SCORE_BLK);
-            for (u32 i = i0; i < i1; ++i) {
-                const PodRegs pod = pod_from_smem(sm.sp, i);
-                const bool same = (pod.gid == cur_gid) && (pod.cls == cur_cls) && (pod.m >= cur_m);
-                if (!same || __any_sync(0xFFFFFFFFu, pod.m > bmin)) {
-                    cur_cls = pod.cls; cur_gid = pod.gid;
+    for (u32 i = 0; i < cn;) {  // i is warp-uniform
+        const PodRegs pod = pod_from_smem(sm.sp, i);
+        const u32 key = (pod.gid << FAST_GID_BITS) | pod.cls;
+        const bool same = key == cur_key;
+        cur_key = key;
 #pragma unroll
-                    for (int j = 0; j < NPL; ++j) {
-                        if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
-                            bool fit;
-                            u32 b;
-                            const u32 raw = hot_eval_mem(s, tables, node[j], pod.cls, pod.m, pod.num, pod.reqM, pod.has_clock, pod.c, pod.reqC, ok[j],
-                                                         cardnum[j], stat[j], fit, b);
-                            bound[j] = fit ? b : 0xFFFFFFFFu;
-                            hi_l[j] = fit ? raw : 0u;
-                            lo_l[j] = fit ? raw : 0xFFFFFFFFu;
-                        }
-                    }
-                    u32 hi = hi_l[0], lo = lo_l[0];
-                    bmin = bound[0];
-#pragma unroll
-                    for (int j = 1; j < NPL; ++j) { hi = max(hi, hi_l[j]); lo = min(lo, lo_l[j]); bmin = min(bmin, bound[j]); }
-                    const u32 hi_w = __reduce_max_sync(0xFFFFFFFFu, hi);
-                    const u32 lo_w = __reduce_min_sync(0xFFFFFFFFu, lo);
-                    u32 cnt_w = 0, best_w = 0xFFFFFFFFu;
-                    if (DECIDE) {
-#pragma unroll
-                        for (int j = NPL - 1; j >= 0; --j) {
-                            const bool fitj = lo_l[j] != 0xFFFFFFFFu;
-                            cnt_w += __popc(__ballot_sync(0xFFFFFFFFu, fitj));
-                            const u32 top = __ballot_sync(0xFFFFFFFFu, fitj && hi_l[j] == hi_w);
-                            if (top) best_w = base + j * 32 + (__ffs(top) - 1);
-                        }
-                    }
-                    mk |= 1u << (i - w0);
-                    if (lane == 0) {
-                        sm.hi_s[warp][i] = hi_w;
-                        sm.lo_s[warp][i] = lo_w;
-                        if (DECIDE) {
-                            sm.cnt_s[warp][i] = cnt_w;
-                            sm.best_s[warp][i] = best_w;
-                        }
-                    }
-                }
-                cur_m = pod.m;
+        for (int j = 0; j < NPL; ++j) {
+            if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
+                bool fit;
+                u32 b;
+                const u32 raw = hot_eval_mem(s, tables, node[j], pod.cls, pod.m, pod.num, pod.reqM, pod.has_clock, pod.c, pod.reqC, ok[j],
+                                             cardnum[j], stat[j], fit, b);
+                bound[j] = fit ? b : 0xFFFFFFFFu;  // a node that stopped fitting never fits again inside the run
+                hi_l[j] = fit ? raw : 0u;
+                lo_l[j] = fit ? raw : 0xFFFFFFFFu;
             }
         }
-        if (lane == 0) sm.mark_s[warp][w0 >> 5] = mk;
+        u32 hi = hi_l[0], lo = lo_l[0], bmin = bound[0];
+#pragma unroll
+        for (int j = 1; j < NPL; ++j) { hi = max(hi, hi_l[j]); lo = min(lo, lo_l[j]); bmin = min(bmin, bound[j]); }
+        const u32 hi_w = __reduce_max_sync(0xFFFFFFFFu, hi);
+        const u32 lo_w = __reduce_min_sync(0xFFFFFFFFu, lo);
+        const u32 wb = __reduce_min_sync(0xFFFFFFFFu, bmin);  // the warp's results hold for every m <= wb of this run
+        u32 cnt_w = 0, best_w = 0xFFFFFFFFu;
+        if (DECIDE) {
+#pragma unroll
+            for (int j = NPL - 1; j >= 0; --j) {
+                const bool fitj = lo_l[j] != 0xFFFFFFFFu;
+                cnt_w += __popc(__ballot_sync(0xFFFFFFFFu, fitj));
+                const u32 top = __ballot_sync(0xFFFFFFFFu, fitj && hi_l[j] == hi_w);
+                if (top) best_w = base + j * 32 + (__ffs(top) - 1);
+            }
+        }
+        if (lane == 0) {
+            sm.hi_s[warp][i] = hi_w;
+            sm.lo_s[warp][i] = lo_w;
+            if (DECIDE) {
+                sm.cnt_s[warp][i] = cnt_w;
+                sm.best_s[warp][i] = best_w;
+            }
+            sm.mark_s[warp][i >> 5] |= 1u << (i & 31);  // this warp's row: no other writer
+        }
+        // look ahead: the first later pod of another run, or beyond the bound
+        u32 k = i + 1;
+        for (;;) {
+            const u32 idx = k + lane;
+            const bool stop = idx >= cn || sm.key_s[idx] != key || sm.m_s[idx] > wb;
+            const u32 bal = __ballot_sync(0xFFFFFFFFu, stop);
+            if (bal) {
+                k += __ffs(bal) - 1;
+                break;
+            }
+            k += 32;
+        }
+        i = k;
     }
     half_sync(bar_id);
     for (u32 i = tid; i < cn; i += HOT_THREADS) {
@@ -998,8 +984,11 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
     }
 }
 
+#ifndef SCORE_MINB
+#define SCORE_MINB 4  // resident CTAs per SM the score pass is compiled for
+#endif
 template <int NPL, bool DECIDE>
-__global__ void __launch_bounds__(HOT_THREADS, 4) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
+__global__ void __launch_bounds__(HOT_THREADS, SCORE_MINB) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
                                                             const u32 *__restrict__ tables, u64 *hilo, u64 *count, u64 *dkey,
                                                             u32 chunk_pods) {  // pods per CTA: a multiple of SCORE_BLK, <= SCORE_CHUNK
     __shared__ ScoreSmem sm;

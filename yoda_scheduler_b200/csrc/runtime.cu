@@ -89,7 +89,9 @@ static int nccl_load() {
 // ------------------------------------------------------------------------------------------
 enum { EV_START = 0, EV_PREP, EV_MAX, EV_SCORE, EV_WRITE, EV_H2D0, EV_H2D1, EV_D2H0, EV_D2H1, EV_COUNT };
 
+#ifndef SCORE_NPL
 #define SCORE_NPL 4  // nodes per lane in the score pass (its per-node state is 7 registers)
+#endif
 
 struct yoda_ctx {
     std::mutex mu;
@@ -137,6 +139,9 @@ struct yoda_ctx {
     // NormalizeScore list scratch
     i64 *d_list = nullptr, *d_lohi = nullptr;
     u32 list_cap = 0;
+    // pinned staging of yoda_fetch_rows / yoda_fetch_row (uint32 score rows are widened from here)
+    u8 *h_rows = nullptr;
+    size_t h_rows_cap = 0;
     // NCCL
     ncclComm_t comm = nullptr;
     u64 *d_agree = nullptr, *h_agree = nullptr;  // one word all-reduced before a sharded DECIDE score pass (see phase1)
@@ -328,6 +333,7 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
     if (c->fw_hctl) cudaFreeHost(c->fw_hctl);
     if (c->h_upd) cudaFreeHost(c->h_upd);
+    if (c->h_rows) cudaFreeHost(c->h_rows);
     if (c->h_req) cudaFreeHost(c->h_req);
     if (c->h_res) cudaFreeHost(c->h_res);
     for (int i = 0; i < EV_COUNT; ++i)
@@ -1198,6 +1204,20 @@ extern "C" int yoda_last_timing(yoda_ctx *c, yoda_timing *t) {
     return YODA_OK;
 }
 
+static int ensure_row_staging(yoda_ctx *c, size_t bytes) {
+    if (bytes <= c->h_rows_cap) return YODA_OK;
+    if (c->h_rows) cudaFreeHost(c->h_rows);
+    c->h_rows = nullptr;
+    c->h_rows_cap = 0;
+    const size_t cap = std::max<size_t>(bytes, 1 << 16);
+    if (cudaMallocHost((void **)&c->h_rows, cap) != cudaSuccess) {
+        cudaGetLastError();
+        return fail(YODA_E_NOMEM, "cudaMallocHost of %zu bytes of row staging failed", cap);
+    }
+    c->h_rows_cap = cap;
+    return YODA_OK;
+}
+
 extern "C" int yoda_fetch_row(yoda_ctx *c, u32 pod, int kind, void *dst, size_t bytes) {
     if (!c || !dst) return fail(YODA_E_ARG, "null argument");
     std::lock_guard<std::mutex> lk(c->mu);
@@ -1210,12 +1230,13 @@ extern "C" int yoda_fetch_row(yoda_ctx *c, u32 pod, int kind, void *dst, size_t 
     switch (kind) {
         case YODA_ROW_FEASIBLE_BITS: src = c->d_bits + (size_t)pod * (c->stride / 32); row = (c->stride / 32) * 4; break;
         case YODA_ROW_RAW:
-            if (c->res_raw32) {  // uint32 on the device, int64 for the caller
+            if (c->res_raw32) {  // uint32 on the device, int64 for the caller: widened out of the pinned staging buffer
                 if (bytes > c->stride * 8) return fail(YODA_E_RANGE, "row kind %d holds %zu bytes, %zu requested", kind, (size_t)c->stride * 8, bytes);
                 const size_t n = bytes / 8;
-                std::vector<u32> tmp(n);
-                CU(cudaMemcpyAsync(tmp.data(), (const u32 *)c->d_raw + (size_t)pod * c->stride, n * 4, cudaMemcpyDeviceToHost, c->stream));
+                TRY(ensure_row_staging(c, n * 4));
+                CU(cudaMemcpyAsync(c->h_rows, (const u32 *)c->d_raw + (size_t)pod * c->stride, n * 4, cudaMemcpyDeviceToHost, c->stream));
                 CU(cudaStreamSynchronize(c->stream));
+                const u32 *tmp = (const u32 *)c->h_rows;
                 for (size_t i = 0; i < n; ++i) ((i64 *)dst)[i] = (i64)tmp[i];
                 return YODA_OK;
             }
@@ -1226,6 +1247,35 @@ extern "C" int yoda_fetch_row(yoda_ctx *c, u32 pod, int kind, void *dst, size_t 
     if (bytes > row) return fail(YODA_E_RANGE, "row kind %d holds %zu bytes, %zu requested", kind, row, bytes);
     CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
+    return YODA_OK;
+}
+
+// The three rows of one pod with a single synchronisation: three async copies into the pinned staging buffer
+// (true DMA, whatever memory the caller's buffers are), then one pass that hands them out.
+extern "C" int yoda_fetch_rows(yoda_ctx *c, u32 pod, u32 n_nodes, uint32_t *bits, int64_t *raw, uint8_t *norm) {
+    if (!c || !bits || !raw || !norm) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (!c->last_full || pod >= c->last_P)
+        return fail(YODA_E_STATE, "no YODA_EVAL_FULL result holds pod %u (last batch: %u pods, full=%d)", pod, c->last_P, (int)c->last_full);
+    if (n_nodes > c->stride) return fail(YODA_E_RANGE, "%u nodes requested, rows hold %llu", n_nodes, (unsigned long long)c->stride);
+    if (n_nodes == 0) return YODA_OK;
+    const size_t words = (n_nodes + 31) / 32, raw_elem = c->res_raw32 ? 4 : 8;
+    const size_t off_raw = (words * 4 + 15) & ~(size_t)15, off_norm = off_raw + (((size_t)n_nodes * raw_elem + 15) & ~(size_t)15);
+    TRY(ensure_row_staging(c, off_norm + n_nodes));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->h_rows, c->d_bits + (size_t)pod * (c->stride / 32), words * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(c->h_rows + off_raw, (const u8 *)c->d_raw + (size_t)pod * c->stride * raw_elem, (size_t)n_nodes * raw_elem, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(c->h_rows + off_norm, c->d_norm + (size_t)pod * c->stride, n_nodes, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    memcpy(bits, c->h_rows, words * 4);
+    if (c->res_raw32) {
+        const u32 *src = (const u32 *)(c->h_rows + off_raw);
+        for (u32 i = 0; i < n_nodes; ++i) raw[i] = (i64)src[i];
+    } else {
+        memcpy(raw, c->h_rows + off_raw, (size_t)n_nodes * 8);
+    }
+    memcpy(norm, c->h_rows + off_norm, n_nodes);
     return YODA_OK;
 }
 

@@ -14,7 +14,11 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#include <atomic>
 #include <fstream>
+#include <functional>
+#include <thread>
 
 #include "synth.hpp"
 #include "yoda_plugin.hpp"
@@ -36,7 +40,7 @@ static uint64_t fnv(uint64_t h, uint64_t v) {
 }
 
 int main(int argc, char **argv) {
-    uint64_t N = 2000, P = 256, pod_seed = synth::SEED + 2, cycles = 16, seq = 0;
+    uint64_t N = 2000, P = 256, pod_seed = synth::SEED + 2, cycles = 16, seq = 0, threads = 16;
     bool checksum = false;
     const char *dump = nullptr;
     for (int i = 1; i < argc; ++i) {
@@ -46,6 +50,7 @@ int main(int argc, char **argv) {
         else if (!strcmp(argv[i], "--pod-seed")) pod_seed = next();
         else if (!strcmp(argv[i], "--cycles")) cycles = next();
         else if (!strcmp(argv[i], "--seq")) seq = next();
+        else if (!strcmp(argv[i], "--threads")) threads = std::max<uint64_t>(1, next());  // framework parallelism (16 in kube-scheduler)
         else if (!strcmp(argv[i], "--checksum")) checksum = true;
         else if (!strcmp(argv[i], "--dump") && i + 1 < argc) dump = argv[++i];
     }
@@ -79,7 +84,7 @@ int main(int argc, char **argv) {
     FakeHandle handle;
     std::string err;
     yoda::Yoda::Options opt;
-    opt.max_nodes = (uint32_t)std::max<uint64_t>(N, 1);
+    opt.max_nodes = (uint32_t)std::max<uint64_t>(N, 1) + 1;  // one spare index for the late node of (2b)
     auto plugin = yoda::Yoda::New(opt, &handle, &err);
     if (!plugin) { fprintf(stderr, "yoda.New failed: %s\n", err.c_str()); return 2; }
     auto t0 = Clock::now();
@@ -114,36 +119,94 @@ int main(int argc, char **argv) {
     yoda_timing tm{};
     yoda_last_timing(plugin->ctx(), &tm);
 
-    // ---- (2) framework path ---------------------------------------------------------------------------
+    // ---- (2) framework path: Filter and Score from `threads` threads at once, as parallelize.Until does ----------
     int mismatches = 0;
     cycles = std::min<uint64_t>(cycles, P);
+    std::vector<double> cycle_times;
+    auto parallel_nodes = [&](size_t n, const std::function<void(size_t)> &f) {
+        std::atomic<size_t> next{0};
+        std::vector<std::thread> pool;
+        for (uint64_t t = 0; t < threads; ++t)
+            pool.emplace_back([&]() {
+                for (size_t i = next.fetch_add(64); i < n; i = next.fetch_add(64))
+                    for (size_t k = i; k < std::min(n, i + 64); ++k) f(k);
+            });
+        for (auto &th : pool) th.join();
+    };
     t0 = Clock::now();
     for (uint64_t p = 0; p < cycles; ++p) {
+        const auto c0 = Clock::now();
         framework::CycleState state;
         const v1::Pod &pod = pods[p];
+        std::vector<uint8_t> fit(nodes.size(), 0);
+        parallel_nodes(nodes.size(), [&](size_t n) {  // findNodesThatPassFilters
+            fit[n] = plugin->Filter(state, pod, *handle.GetNodeInfo(nodes[n].scv.Name)).IsSuccess();
+        });
         std::vector<std::string> feasible;
-        for (const auto &nd : nodes)  // findNodesThatPassFilters
-            if (plugin->Filter(state, pod, *handle.GetNodeInfo(nd.scv.Name)).IsSuccess()) feasible.push_back(nd.scv.Name);
+        for (size_t n = 0; n < nodes.size(); ++n)
+            if (fit[n]) feasible.push_back(nodes[n].scv.Name);
         auto pf = plugin->PostFilter(state, pod);  // max-collection hook
         if (!pf.second.IsSuccess()) { mismatches++; continue; }
         int32_t chosen = -1;
         if (!feasible.empty()) {
-            framework::NodeScoreList scores;
-            for (const auto &nm : feasible) {  // RunScorePlugins
-                auto sc = plugin->Score(state, pod, nm);
-                if (!sc.second.IsSuccess()) { mismatches++; break; }
-                scores.push_back({nm, sc.first});
-            }
+            framework::NodeScoreList scores(feasible.size());
+            std::atomic<int> bad{0};
+            parallel_nodes(feasible.size(), [&](size_t k) {  // RunScorePlugins
+                auto sc = plugin->Score(state, pod, feasible[k]);
+                if (!sc.second.IsSuccess()) bad++;
+                scores[k] = {feasible[k], sc.first};
+            });
+            mismatches += bad.load();
             plugin->NormalizeScore(state, pod, scores);
             int64_t best = -1;
             for (const auto &s : scores)  // selectHost with the deterministic tie-break of the harness
                 if (s.Score > best) { best = s.Score; chosen = plugin->NodeIndex(s.Name); }
         }
+        cycle_times.push_back(ms_since(c0));
+        state.Lock();
         auto mx = std::dynamic_pointer_cast<yoda::Data>(state.Read("Max"));
+        state.Unlock();
         if (chosen != batch[p].chosen || feasible.size() != batch[p].feasible || !mx || mx->Value.MaxFreeMemory != batch[p].max_free_memory)
             mismatches++;
     }
     const double cycle_ms = cycles ? ms_since(t0) / (double)cycles : 0.0;
+    std::sort(cycle_times.begin(), cycle_times.end());
+    const double cycle_p50 = cycle_times.empty() ? 0.0 : cycle_times[cycle_times.size() / 2];
+    const double cycle_p99 = cycle_times.empty() ? 0.0 : cycle_times[std::min(cycle_times.size() - 1, (size_t)(cycle_times.size() * 0.99))];
+
+    // ---- (2b) a node whose Scv arrives between Filter and Score of a cycle is not part of that cycle: Score must
+    //          answer "not found" (as the reference does for a node without Scv), never index past the memo; and
+    //          a refused Scv (TotalMemorySum == 0) takes the node's previous record out of service
+    if (P > 0) {
+        framework::CycleState state;
+        const v1::Pod &pod = pods[0];
+        plugin->Filter(state, pod, *handle.GetNodeInfo(nodes[0].scv.Name));
+        plugin->PostFilter(state, pod);
+        scv::Scv late = nodes[0].scv;
+        late.Name = "late-node";
+        framework::NodeInfo li;
+        li.node.Name = late.Name;
+        handle.infos[late.Name] = li;
+        if (N + 1 <= opt.max_nodes) {
+            plugin->OnScvUpsert(late);
+            auto sc = plugin->Score(state, pod, late.Name);
+            if (sc.second.IsSuccess() || sc.second.message.find("not found") == std::string::npos) mismatches++;
+            if (plugin->Filter(state, pod, li).IsSuccess()) mismatches++;
+            plugin->OnScvDelete(late.Name);
+        }
+        size_t victim = 0;
+        while (victim < nodes.size() && !nodes[victim].has_scv) ++victim;
+        if (victim < nodes.size()) {
+            scv::Scv broken = nodes[victim].scv;
+            broken.Status.TotalMemorySum = 0;
+            if (plugin->OnScvUpsert(broken).IsSuccess()) mismatches++;
+            framework::CycleState st2;
+            auto f = plugin->Filter(st2, pod, *handle.GetNodeInfo(broken.Name));
+            if (f.IsSuccess() || f.message.find("rejected") == std::string::npos) mismatches++;
+            plugin->OnScvUpsert(nodes[victim].scv);  // repaired
+        }
+        plugin->Sync();
+    }
 
     // ---- (3) sequential commit: one device pass for the first `seq` pods against the real thing -- one
     //         framework cycle per pod with the pod assumed onto its node (OnPodAdd) before the next cycle
@@ -189,8 +252,8 @@ int main(int argc, char **argv) {
         for (const auto &r : batch) f << r.chosen << " " << r.feasible << " " << r.lowest << " " << r.highest << " " << r.max_free_memory << "\n";
     }
     printf("{\"nodes\": %llu, \"pods\": %llu, \"load_ms\": %.3f, \"batch_ms\": %.3f, \"batch_device_ms\": %.3f, \"evals_per_s\": %.4g, "
-           "\"framework_cycle_ms\": %.3f, \"cycles_checked\": %llu, \"seq_pods\": %llu, \"seq_ms\": %.3f, \"seq_mismatches\": %d, \"mismatches\": %d, \"path\": %u}\n",
-           (unsigned long long)N, (unsigned long long)P, load_ms, batch_ms, tm.total_ms, (double)N * (double)P / (batch_ms * 1e-3), cycle_ms,
-           (unsigned long long)cycles, (unsigned long long)seq, seq_ms, seq_mismatches, mismatches, tm.path);
+           "\"framework_cycle_ms\": %.3f, \"framework_cycle_p50_ms\": %.3f, \"framework_cycle_p99_ms\": %.3f, \"threads\": %llu, \"cycles_checked\": %llu, \"seq_pods\": %llu, \"seq_ms\": %.3f, \"seq_mismatches\": %d, \"mismatches\": %d, \"path\": %u}\n",
+           (unsigned long long)N, (unsigned long long)P, load_ms, batch_ms, tm.total_ms, (double)N * (double)P / (batch_ms * 1e-3), cycle_ms, cycle_p50, cycle_p99,
+           (unsigned long long)threads, (unsigned long long)cycles, (unsigned long long)seq, seq_ms, seq_mismatches, mismatches, tm.path);
     return mismatches ? 1 : 0;
 }

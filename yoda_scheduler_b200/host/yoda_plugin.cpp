@@ -76,24 +76,35 @@ uint32_t Yoda::index_of(const std::string &name) {
     index_.emplace(name, idx);
     names_.push_back(name);
     has_scv_.push_back(0);
+    reject_.emplace_back();
     alloc_.push_back(0);
     return idx;
 }
 int32_t Yoda::NodeIndex(const std::string &name) const {
+    std::shared_lock<std::shared_mutex> lk(mu_);
     auto it = index_.find(name);
     return it == index_.end() ? -1 : (int32_t)it->second;
 }
 
 // ---- informer events ---------------------------------------------------------------------------
 Status Yoda::OnScvUpsert(const scv::Scv &s) {
-    std::lock_guard<std::mutex> lk(mu_);
+    std::unique_lock<std::shared_mutex> lk(mu_);
     const uint32_t idx = index_of(s.Name);
     yoda_node_record rec{};
     rec.card_number = s.Status.CardNumber;
     rec.free_memory_sum = s.Status.FreeMemorySum;
     rec.total_memory_sum = s.Status.TotalMemorySum;
     rec.n_cards = (uint32_t)s.Status.CardList.size();
-    if (rec.n_cards > YODA_MAX_CARDS) return NewStatus(framework::Error, "Node:" + s.Name + " has more than 8 cards");
+    // A refused object (more than 8 cards; TotalMemorySum == 0, where the reference would panic) must not leave the
+    // node answering from its previous record: it loses its SCV, with the reason kept for Filter's message.
+    auto refuse = [&](const std::string &why) {
+        yoda_node_remove(ctx_, idx);
+        has_scv_[idx] = 0;
+        reject_[idx] = why;
+        dirty_ = true;
+        return NewStatus(framework::Error, why);
+    };
+    if (rec.n_cards > YODA_MAX_CARDS) return refuse("Node:" + s.Name + " has more than 8 cards");
     for (uint32_t g = 0; g < rec.n_cards; ++g) {
         const scv::Card &c = s.Status.CardList[g];
         if (c.Health == "Healthy") rec.healthy_mask |= 1u << g;  // filter.go:53,57
@@ -104,16 +115,18 @@ Status Yoda::OnScvUpsert(const scv::Scv &s) {
         rec.bandwidth[g] = c.Bandwidth;
         rec.power[g] = c.Power;
     }
-    if (yoda_node_upsert(ctx_, idx, &rec) != YODA_OK) return NewStatus(framework::Error, yoda_last_error());
+    if (yoda_node_upsert(ctx_, idx, &rec) != YODA_OK) return refuse(yoda_last_error());
     has_scv_[idx] = 1;
+    reject_[idx].clear();
     dirty_ = true;
     return NewStatus(framework::Success);
 }
 void Yoda::OnScvDelete(const std::string &nodeName) {
-    std::lock_guard<std::mutex> lk(mu_);
+    std::unique_lock<std::shared_mutex> lk(mu_);
     const uint32_t idx = index_of(nodeName);
     yoda_node_remove(ctx_, idx);
     has_scv_[idx] = 0;
+    reject_[idx].clear();
     dirty_ = true;
 }
 static uint64_t pod_memory(const v1::Pod &pod, bool *has) {
@@ -125,7 +138,7 @@ void Yoda::OnPodAdd(const std::string &nodeName, const v1::Pod &pod) {
     bool has;
     const uint64_t m = pod_memory(pod, &has);
     if (!has) return;
-    std::lock_guard<std::mutex> lk(mu_);
+    std::unique_lock<std::shared_mutex> lk(mu_);
     const uint32_t idx = index_of(nodeName);
     alloc_[idx] += m;  // wraps like the Go uint64 sum (algorithm.go:78)
     yoda_node_set_alloc(ctx_, idx, alloc_[idx]);
@@ -135,14 +148,17 @@ void Yoda::OnPodDelete(const std::string &nodeName, const v1::Pod &pod) {
     bool has;
     const uint64_t m = pod_memory(pod, &has);
     if (!has) return;
-    std::lock_guard<std::mutex> lk(mu_);
+    std::unique_lock<std::shared_mutex> lk(mu_);
     const uint32_t idx = index_of(nodeName);
     alloc_[idx] -= m;
     yoda_node_set_alloc(ctx_, idx, alloc_[idx]);
     dirty_ = true;
 }
 Status Yoda::Sync() {
-    std::lock_guard<std::mutex> lk(mu_);
+    std::unique_lock<std::shared_mutex> lk(mu_);
+    return sync_locked();
+}
+Status Yoda::sync_locked() {
     if (dirty_) {
         if (yoda_commit(ctx_, nullptr) != YODA_OK) return NewStatus(framework::Error, yoda_last_error());
         dirty_ = false;
@@ -153,10 +169,13 @@ Status Yoda::Sync() {
 // ---- per-cycle memo ----------------------------------------------------------------------------
 struct Yoda::Memo : framework::StateData {
     yoda_pod_result res{};
-    uint32_t n_nodes = 0;
+    uint32_t n_nodes = 0;            // nodes the evaluation covered; indices >= n_nodes were registered later
+    std::vector<uint8_t> has;        // has_scv_[0..n_nodes) as of the evaluation: the cycle's frozen view
+    std::vector<std::string> reject;
     std::vector<uint32_t> bits;
     std::vector<int64_t> raw;
     std::vector<uint8_t> norm;
+    bool known(int32_t idx) const { return idx >= 0 && (uint32_t)idx < n_nodes && has[idx]; }
     bool feasible(uint32_t idx) const { return idx < n_nodes && ((bits[idx >> 5] >> (idx & 31)) & 1u); }
 };
 static const char *kMemoKey = "yoda/b200";
@@ -167,22 +186,23 @@ std::shared_ptr<Yoda::Memo> Yoda::memo(framework::CycleState &state, const v1::P
     state.Lock();
     auto have = std::dynamic_pointer_cast<Memo>(state.Read(kMemoKey));
     if (!have) {
-        Status s = Sync();
+        std::unique_lock<std::shared_mutex> lk(mu_);
+        Status s = sync_locked();
         auto m = std::make_shared<Memo>();
         if (s.IsSuccess()) {
-            std::lock_guard<std::mutex> lk(mu_);
             const yoda_pod_req req = Requirement(pod);
             uint32_t n = 0;
             if (yoda_eval_batch(ctx_, &req, 1, YODA_EVAL_FULL, &m->res) != YODA_OK || yoda_node_count(ctx_, &n) != YODA_OK) {
                 s = NewStatus(framework::Error, yoda_last_error());
             } else {
+                n = std::min<uint32_t>(n, (uint32_t)has_scv_.size());
                 m->n_nodes = n;
+                m->has.assign(has_scv_.begin(), has_scv_.begin() + n);
+                m->reject.assign(reject_.begin(), reject_.begin() + n);
                 m->bits.assign((n + 31) / 32 + 1, 0);
                 m->raw.assign(n + 1, 0);
                 m->norm.assign(n + 1, 0);
-                if (n && (yoda_fetch_row(ctx_, 0, YODA_ROW_FEASIBLE_BITS, m->bits.data(), ((n + 31) / 32) * 4) != YODA_OK ||
-                          yoda_fetch_row(ctx_, 0, YODA_ROW_RAW, m->raw.data(), (size_t)n * 8) != YODA_OK ||
-                          yoda_fetch_row(ctx_, 0, YODA_ROW_NORM, m->norm.data(), n) != YODA_OK))
+                if (n && yoda_fetch_rows(ctx_, 0, n, m->bits.data(), m->raw.data(), m->norm.data()) != YODA_OK)
                     s = NewStatus(framework::Error, yoda_last_error());
             }
         }
@@ -205,8 +225,11 @@ Status Yoda::Filter(framework::CycleState &state, const v1::Pod &pod, const fram
     auto m = memo(state, pod, &st);
     if (!m) return st;
     const int32_t idx = NodeIndex(name);
-    if (idx < 0 || !has_scv_[idx])  // cache.Get failed (:81-84)
+    if (!m->known(idx)) {  // cache.Get failed (:81-84); also a node registered after this cycle's evaluation
+        if (idx >= 0 && (uint32_t)idx < m->n_nodes && !m->reject[idx].empty())
+            return NewStatus(framework::Unschedulable, "Node:" + name + " Scv rejected: " + m->reject[idx]);
         return NewStatus(framework::Unschedulable, "Node:" + name + " Scv.core.run-linux.com \"" + name + "\" not found");
+    }
     if (m->feasible((uint32_t)idx)) return NewStatus(framework::Success, "");
     return NewStatus(framework::Unschedulable, "Node:" + name);  // :92
 }
@@ -237,14 +260,17 @@ bool Yoda::Less(const framework::QueuedPodInfo &a, const framework::QueuedPodInf
 std::pair<int64_t, Status> Yoda::Score(framework::CycleState &state, const v1::Pod &p, const std::string &nodeName) {
     if (!handle_ || !handle_->GetNodeInfo(nodeName))  // :111-114
         return {0, NewStatus(framework::Error, "getting node \"" + nodeName + "\" from Snapshot: nodeinfo not found for node name \"" + nodeName + "\"")};
-    const int32_t idx = NodeIndex(nodeName);
-    if (idx < 0 || !has_scv_[idx])  // :117-122
-        return {0, NewStatus(framework::Error, "Score Node Error: Scv.core.run-linux.com \"" + nodeName + "\" not found")};
-    if (!std::dynamic_pointer_cast<Data>(state.Read("Max")))  // algorithm.go:29-37: "Max" must have been written
-        return {0, NewStatus(framework::Error, "Score Node Error: not found")};
     Status st;
     auto m = memo(state, p, &st);
     if (!m) return {0, NewStatus(framework::Error, "Score Node Error: " + st.message)};
+    const int32_t idx = NodeIndex(nodeName);
+    if (!m->known(idx))  // :117-122; a node registered after the cycle's evaluation is not part of it either
+        return {0, NewStatus(framework::Error, "Score Node Error: Scv.core.run-linux.com \"" + nodeName + "\" not found")};
+    state.Lock();
+    const bool have_max = std::dynamic_pointer_cast<Data>(state.Read("Max")) != nullptr;
+    state.Unlock();
+    if (!have_max)  // algorithm.go:29-37: "Max" must have been written
+        return {0, NewStatus(framework::Error, "Score Node Error: not found")};
     return {m->raw[idx], NewStatus(framework::Success, "")};
 }
 
@@ -253,12 +279,15 @@ std::pair<int64_t, Status> Yoda::Score(framework::CycleState &state, const v1::P
 // the list is rescaled on the device as given.  Panics (throws) on an empty list like the Go code.
 Status Yoda::NormalizeScore(framework::CycleState &state, const v1::Pod &pod, framework::NodeScoreList &scores) {
     if (scores.empty()) throw std::out_of_range("index out of range [0] with length 0");  // scores[0], :135
+    state.Lock();
     auto m = std::dynamic_pointer_cast<Memo>(state.Read(kMemoKey));
+    state.Unlock();
     bool own = m && scores.size() == m->res.feasible;
     std::vector<int32_t> idx(scores.size(), -1);
     for (size_t i = 0; own && i < scores.size(); ++i) {
         idx[i] = NodeIndex(scores[i].Name);
-        own = idx[i] >= 0 && m->feasible((uint32_t)idx[i]) && m->raw[idx[i]] == scores[i].Score;
+        // norm == 255 marks a rescale that wrapped outside [0,100]: only the exact list path returns the wrapped int64
+        own = idx[i] >= 0 && m->feasible((uint32_t)idx[i]) && m->raw[idx[i]] == scores[i].Score && m->norm[idx[i]] != 255;
     }
     if (own) {
         for (size_t i = 0; i < scores.size(); ++i) scores[i].Score = m->norm[idx[i]];
@@ -267,7 +296,7 @@ Status Yoda::NormalizeScore(framework::CycleState &state, const v1::Pod &pod, fr
     std::vector<int64_t> v(scores.size());
     for (size_t i = 0; i < scores.size(); ++i) v[i] = scores[i].Score;
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::unique_lock<std::shared_mutex> lk(mu_);
         if (yoda_normalize_scores(ctx_, v.data(), (uint32_t)v.size()) != YODA_OK) return NewStatus(framework::Error, yoda_last_error());
     }
     for (size_t i = 0; i < scores.size(); ++i) scores[i].Score = v[i];
@@ -277,19 +306,17 @@ Status Yoda::NormalizeScore(framework::CycleState &state, const v1::Pod &pod, fr
 
 // ---- batch path ----------------------------------------------------------------------------------
 Status Yoda::EvalBatch(const std::vector<v1::Pod> &pods, bool full, std::vector<yoda_pod_result> *out) {
-    Status s = Sync();
-    if (!s.IsSuccess()) return s;
     std::vector<yoda_pod_req> reqs(pods.size());
     for (size_t i = 0; i < pods.size(); ++i) reqs[i] = Requirement(pods[i]);
     out->assign(pods.size(), yoda_pod_result{});
-    std::lock_guard<std::mutex> lk(mu_);
+    std::unique_lock<std::shared_mutex> lk(mu_);
+    Status s = sync_locked();
+    if (!s.IsSuccess()) return s;
     if (yoda_eval_batch(ctx_, reqs.data(), (uint32_t)reqs.size(), full ? YODA_EVAL_FULL : YODA_EVAL_DECIDE, out->data()) != YODA_OK)
         return NewStatus(framework::Error, yoda_last_error());
     return NewStatus(framework::Success);
 }
 Status Yoda::EvalSequential(const std::vector<v1::Pod> &pods, std::vector<yoda_pod_result> *out, std::vector<uint32_t> *order_out) {
-    Status s = Sync();
-    if (!s.IsSuccess()) return s;
     std::vector<yoda_pod_req> reqs(pods.size());
     std::vector<int64_t> pri(pods.size());
     for (size_t i = 0; i < pods.size(); ++i) {
@@ -299,7 +326,9 @@ Status Yoda::EvalSequential(const std::vector<v1::Pod> &pods, std::vector<yoda_p
     std::vector<uint32_t> order(pods.size());
     out->assign(pods.size(), yoda_pod_result{});
     if (pods.empty()) return NewStatus(framework::Success);
-    std::lock_guard<std::mutex> lk(mu_);
+    std::unique_lock<std::shared_mutex> lk(mu_);
+    Status s = sync_locked();
+    if (!s.IsSuccess()) return s;
     if (yoda_queue_order(ctx_, pri.data(), (uint32_t)pri.size(), order.data()) != YODA_OK ||
         yoda_eval_sequential(ctx_, reqs.data(), (uint32_t)reqs.size(), order.data(), out->data()) != YODA_OK)
         return NewStatus(framework::Error, yoda_last_error());
@@ -307,7 +336,7 @@ Status Yoda::EvalSequential(const std::vector<v1::Pod> &pods, std::vector<yoda_p
     return NewStatus(framework::Success);
 }
 int Yoda::FetchRow(uint32_t pod, int kind, void *dst, size_t bytes) {
-    std::lock_guard<std::mutex> lk(mu_);
+    std::unique_lock<std::shared_mutex> lk(mu_);
     return yoda_fetch_row(ctx_, pod, kind, dst, bytes);
 }
 }  // namespace yoda

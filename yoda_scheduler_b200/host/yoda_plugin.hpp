@@ -5,6 +5,7 @@
 // the equivalent Go source is under go/).
 #pragma once
 #include <optional>
+#include <shared_mutex>
 
 #include "../../include/yoda_b200.h"
 #include "framework.hpp"
@@ -59,8 +60,14 @@ class Yoda {
     int FetchRow(uint32_t pod, int kind, void *dst, size_t bytes);
     static yoda_pod_req Requirement(const v1::Pod &pod);  // label parsing, filter.go:11-50
     int32_t NodeIndex(const std::string &name) const;     // -1 if never seen
-    const std::string &NodeName(uint32_t idx) const { return names_[idx]; }
-    uint32_t NodeCount() const { return (uint32_t)names_.size(); }
+    std::string NodeName(uint32_t idx) const {
+        std::shared_lock<std::shared_mutex> lk(mu_);
+        return names_[idx];
+    }
+    uint32_t NodeCount() const {
+        std::shared_lock<std::shared_mutex> lk(mu_);
+        return (uint32_t)names_.size();
+    }
     yoda_ctx *ctx() { return ctx_; }
 
    private:
@@ -71,12 +78,16 @@ class Yoda {
 
     const framework::Handle *handle_ = nullptr;
     yoda_ctx *ctx_ = nullptr;
-    std::mutex mu_;
+    // mu_ guards everything below: event handlers and evaluations take it exclusively, the per-node lookups of
+    // Filter / Score / NormalizeScore (16 framework threads at once) take it shared
+    mutable std::shared_mutex mu_;
     std::unordered_map<std::string, uint32_t> index_;
     std::vector<std::string> names_;
     std::vector<uint8_t> has_scv_;
+    std::vector<std::string> reject_;  // why the node's last Scv was refused ("" = accepted)
     std::vector<uint64_t> alloc_;
     bool dirty_ = false;
+    framework::Status sync_locked();
 };
 
 // sort.Less / sort.GetPodPriority (sort.go:8-18)

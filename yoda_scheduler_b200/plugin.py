@@ -116,7 +116,15 @@ class Yoda:
                              ("Bandwidth", "bandwidth"), ("Power", "power")):
                 rec[dst][0, g] = c[src]
         rec["healthy_mask"] = hm
-        self.ctx.upsert(i, rec)
+        try:
+            self.ctx.upsert(i, rec)
+        except api.YodaError:
+            # refused (more than 8 cards; TotalMemorySum == 0, where the reference would panic): the node must not keep
+            # answering from its previous record
+            self.ctx.remove(i)
+            self.has_scv[i] = False
+            self.dirty = True
+            raise
         self.has_scv[i] = True
         self.dirty = True
 
@@ -149,16 +157,23 @@ class Yoda:
                 self.sync()
                 res = self.ctx.eval(labels.pods_to_requests([pod.labels]), api.EVAL_FULL)
                 n = self.ctx.node_count()
+                n = min(n, len(self.has_scv))
+                # the cycle's frozen view: rows plus has_scv as of the evaluation; a node registered later is not part of it
                 state[_MEMO] = (res[0], self.ctx.fetch_row(0, api.ROW_FEASIBLE_BITS, n), self.ctx.fetch_row(0, api.ROW_RAW, n),
-                                self.ctx.fetch_row(0, api.ROW_NORM, n))
+                                self.ctx.fetch_row(0, api.ROW_NORM, n), list(self.has_scv[:n]))
             return state[_MEMO]
+
+    @staticmethod
+    def _known(memo, i) -> bool:
+        return i is not None and i < len(memo[4]) and memo[4][i]
 
     # ---- plugin methods -----------------------------------------------------------------------
     def filter(self, state: CycleState, pod: Pod, node: NodeInfo) -> Status:
         """scheduler.go:76-93"""
-        _, bits, _, _ = self._memo(state, pod)
+        memo = self._memo(state, pod)
+        bits = memo[1]
         i = self.index.get(node.name)
-        if i is None or not self.has_scv[i]:
+        if not self._known(memo, i):
             return Status(UNSCHEDULABLE, f'Node:{node.name} Scv.core.run-linux.com "{node.name}" not found')   # :83
         if i < len(bits) and bits[i]:
             return Status(SUCCESS, "")
@@ -180,12 +195,13 @@ class Yoda:
         """scheduler.go:109-130"""
         if self.handle.get(node_name) is None:
             return 0, Status(ERROR, f'getting node "{node_name}" from Snapshot: nodeinfo not found for node name "{node_name}"')
+        memo = self._memo(state, pod)
         i = self.index.get(node_name)
-        if i is None or not self.has_scv[i]:
+        if not self._known(memo, i):                            # :117-122; also a node registered after the evaluation
             return 0, Status(ERROR, f'Score Node Error: Scv.core.run-linux.com "{node_name}" not found')
         if "Max" not in state:                                  # algorithm.go:29-33
             return 0, Status(ERROR, "Score Node Error: not found")
-        return int(self._memo(state, pod)[2][i]), Status(SUCCESS, "")
+        return int(memo[2][i]), Status(SUCCESS, "")
 
     def normalize_score(self, state: CycleState, pod: Pod, scores: List[NodeScore]) -> Optional[Status]:
         """scheduler.go:132-157: in place, returns None (nil); an empty list raises like the Go index panic."""
@@ -196,7 +212,7 @@ class Yoda:
         if own:
             for s in scores:
                 i = self.index.get(s.name)
-                if i is None or not memo[1][i] or int(memo[2][i]) != s.score:
+                if i is None or i >= len(memo[1]) or not memo[1][i] or int(memo[2][i]) != s.score or int(memo[3][i]) == 255:
                     own = False
                     break
         if own:
