@@ -185,6 +185,37 @@ int yoda_eval_sequential(yoda_ctx *ctx, const yoda_pod_req *pods, uint32_t n_pod
  * arrival order (Less is false both ways for them). */
 int yoda_queue_order(yoda_ctx *ctx, const int64_t *priority, uint32_t n, uint32_t *order);
 
+/* ---- framework tail: what kube-scheduler v1.20 does around the plugin for each pod, applied on the
+ *      device to the matrices of the last YODA_EVAL_FULL batch -- for the stand-alone batch mode; behind the real
+ *      framework these steps stay the framework's.  Replaces, per pod: numFeasibleNodesToFind + the round-robin
+ *      node walk of findNodesThatPassFilters (percentageOfNodesToScore, deploy/yoda-scheduler.yaml:18),
+ *      Yoda.NormalizeScore over the nodes found (scheduler.go:132-157), the plugin weight (deploy/yoda-scheduler.yaml:30)
+ *      plus the other plugins' scores, and selectHost's reservoir tie-break with a seeded generator in place of
+ *      math/rand (cmd/scheduler/main.go:13 seeds it from the clock).  Nodes are taken strictly in visiting order,
+ *      one of the outcomes upstream's 16 filter goroutines can produce. ---- */
+#define YODA_TAIL_CHAIN 1u /* pods are consecutive cycles: each starts its node walk where the previous one stopped */
+typedef struct {
+    uint32_t weight;       /* plugin weight; 300 in the shipped profile */
+    int32_t percentage;    /* percentageOfNodesToScore; <= 0 = adaptive (50 - nodes/125, at least 5) */
+    uint64_t seed;         /* tie-break generator: rand.Intn(k) := SplitMix64(seed, pod, k) % k */
+    uint32_t start_index;  /* nextStartNodeIndex of the first (YODA_TAIL_CHAIN) or of every pod */
+    uint32_t flags;        /* YODA_TAIL_* */
+    const int64_t *other_scores; /* host, one per node: what the other plugins add to a node's total; NULL = 0 */
+} yoda_tail_config;
+typedef struct {
+    int32_t chosen;          /* global node index, -1 if no node passed Filter */
+    uint32_t sampled;        /* feasible nodes found (<= numFeasibleNodesToFind) */
+    uint32_t processed;      /* nodes visited; the next cycle starts at (start + processed) % nodes */
+    uint32_t start;          /* where this pod's walk started */
+    int64_t lowest, highest; /* of the nodes found, as NormalizeScore used them (0, 0 when scoring was skipped: < 2 nodes) */
+    int64_t top;             /* winning total = normalized * weight + other */
+    uint32_t ties, reserved; /* nodes holding the winning total */
+} yoda_tail_result;
+uint32_t yoda_num_feasible_nodes_to_find(uint32_t num_all_nodes, int32_t percentage);
+/* out: one entry per pod of the last YODA_EVAL_FULL batch; next_start (may be NULL): nextStartNodeIndex afterwards.
+ * Unsharded contexts only. */
+int yoda_framework_tail(yoda_ctx *ctx, const yoda_tail_config *cfg, yoda_tail_result *out, uint32_t *next_start);
+
 /* No counterpart in the reference.  The same rescale for callers that may not allocate: no
  * context, no cudaMalloc/cudaFree, no host allocation -- the only scratch is a fixed 16 KiB array
  * inside the library image (resident on every GPU that loads the library, until exit), which

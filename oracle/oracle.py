@@ -48,6 +48,10 @@ def lib():
         L.ora_pod_priority.restype = C.c_int64
         L.ora_pod_priority.argtypes = [C.c_char_p]
         L.ora_queue_order.argtypes = [C.c_uint32, C.c_void_p, C.c_void_p]
+        L.ora_num_feasible_nodes_to_find.restype = C.c_uint32
+        L.ora_num_feasible_nodes_to_find.argtypes = [C.c_uint32, C.c_int32]
+        L.ora_framework_tail.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int32, C.c_uint64, C.c_uint32,
+                                         C.c_int] + [C.c_void_p] * 9
         _lib = L
     return _lib
 
@@ -66,6 +70,10 @@ def normalize_score(scores: Sequence[int]) -> list:
     if rc:
         raise IndexError("NormalizeScore on an empty list panics in the reference (scheduler.go:135)")
     return a.tolist()
+
+
+def num_feasible_nodes_to_find(n_nodes: int, percentage: int = 0) -> int:
+    return int(lib().ora_num_feasible_nodes_to_find(n_nodes, percentage))
 
 
 def pod_priority(label: Optional[str]) -> int:
@@ -159,6 +167,23 @@ class OracleCluster:
         rc = lib().ora_score_with_max(self._h, enc("scv/number"), enc("scv/memory"), enc("scv/clock"), mx.ctypes.data, feas.ctypes.data, raw.ctypes.data)
         assert rc == 0, rc
         return feas, raw
+
+    def framework_tail(self, pods: Sequence[dict], weight: int = 300, percentage: int = 0, seed: int = 0, start_index: int = 0, chain: bool = False,
+                       other=None) -> dict:
+        """What kube-scheduler v1.20 does around the plugin per pod: sample feasible nodes round-robin, score + normalize the sample,
+        weight, add the other plugins' scores, seeded reservoir tie-break (ora_framework_tail)."""
+        P = len(pods)
+        num = _cstr_array([d.get("scv/number") for d in pods])
+        mem = _cstr_array([d.get("scv/memory") for d in pods])
+        clk = _cstr_array([d.get("scv/clock") for d in pods])
+        o = None if other is None else np.ascontiguousarray(other, dtype=np.int64)
+        out = {"chosen": np.zeros(P, np.int32), "sampled": np.zeros(P, np.uint32), "processed": np.zeros(P, np.uint32), "start": np.zeros(P, np.uint32),
+               "lowest": np.zeros(P, np.int64), "highest": np.zeros(P, np.int64), "top": np.zeros(P, np.int64), "ties": np.zeros(P, np.uint32)}
+        rc = lib().ora_framework_tail(self._h, P, C.cast(num, C.c_void_p), C.cast(mem, C.c_void_p), C.cast(clk, C.c_void_p), weight, percentage,
+                                      C.c_uint64(seed & (2**64 - 1)), start_index, int(chain), _p(o), *[_p(out[k]) for k in
+                                      ("chosen", "sampled", "processed", "start", "lowest", "highest", "top", "ties")])
+        assert rc == 0, rc
+        return out
 
     def eval_sequential(self, pods: Sequence[dict], order=None) -> dict:
         """Single-pod cycles in `order`, each pod assumed onto its chosen node before the next one."""

@@ -736,3 +736,112 @@ int ora_eval_sequential(ora_cluster *cl, uint32_t n_pods, const char *const *num
     free(pods); free(feas); free(raw); free(list); free(orig_np);
     return rc;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * Framework tail: what kube-scheduler v1.20.0 does around the plugin for one pod.
+ * [3P] k8s.io/kubernetes v1.20.0 pkg/scheduler/core/generic_scheduler.go is not under /root/reference
+ * (un-vendored module pinned at go.mod:12); restated from its published algorithm:
+ *   numFeasibleNodesToFind: all nodes if < 100 of them or percentage >= 100; percentage <= 0 -> adaptive
+ *     50 - numAllNodes/125, floor 5; result numAllNodes*percentage/100, floor 100.
+ *   findNodesThatPassFilters: nodes are visited round-robin from nextStartNodeIndex until that many feasible
+ *     ones are found; nextStartNodeIndex advances by the number of nodes visited.  (Upstream visits them from
+ *     16 goroutines, so which nodes make the cut is a race; this restatement -- like the device version --
+ *     takes them strictly in visiting order, which is one of the outcomes the race can produce.)
+ *   prioritizeNodes: Score + NormalizeScore over the nodes found (scheduler.go:109-157 for Yoda), times the
+ *     plugin weight (300, deploy/yoda-scheduler.yaml:30), plus the other plugins' weighted scores (here: an
+ *     optional per-node addend).  With exactly one feasible node scoring is skipped.
+ *   selectHost: highest total, ties broken by reservoir sampling -- rand.Intn(cnt) == 0 replaces the
+ *     candidate; here rand.Intn(k) is SplitMix64(seed, pod, k) % k so that runs can be compared.
+ * CollectMaxValues still sees every SCV of the cluster (collection.go:39-51): sampling does not touch it.
+ * ------------------------------------------------------------------------------------------------ */
+static uint64_t tail_sm64(uint64_t x) {
+    uint64_t z = x + 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+static uint64_t tail_rand(uint64_t seed, uint64_t pod, uint64_t k) { return tail_sm64(tail_sm64(tail_sm64(seed) + pod) + k); }
+
+uint32_t ora_num_feasible_nodes_to_find(uint32_t num_all_nodes, int32_t percentage) {
+    const int32_t all = (int32_t)num_all_nodes;
+    if (all < 100 || percentage >= 100) return num_all_nodes;
+    int32_t adaptive = percentage;
+    if (adaptive <= 0) {
+        adaptive = 50 - all / 125;
+        if (adaptive < 5) adaptive = 5;
+    }
+    const int32_t num = (int32_t)((int64_t)all * adaptive / 100);
+    return num < 100 ? 100u : (uint32_t)num;
+}
+
+/* out arrays are indexed by pod: chosen (-1 = no feasible node), sampled (feasible nodes found), processed (nodes
+ * visited), start (the pod's own start index), lowest/highest (of the sampled list, after lowest--; 0/0 when scoring
+ * was skipped), top (winning total), ties (nodes holding it).  chain != 0: pods are consecutive cycles, each starting
+ * where the previous stopped; otherwise every pod starts at start_index.  other: per-node addend or NULL. */
+int ora_framework_tail(const ora_cluster *cl, uint32_t n_pods, const char *const *number, const char *const *memory,
+                       const char *const *clock, uint32_t weight, int32_t percentage, uint64_t seed, uint32_t start_index,
+                       int chain, const int64_t *other, int32_t *chosen, uint32_t *sampled, uint32_t *processed,
+                       uint32_t *start, int64_t *lowest, int64_t *highest, int64_t *top, uint32_t *ties) {
+    const uint32_t N = cl->n_nodes;
+    const uint32_t want = ora_num_feasible_nodes_to_find(N, percentage);
+    uint32_t *found = (uint32_t *)malloc(sizeof(uint32_t) * (N ? N : 1));
+    int64_t *list = (int64_t *)malloc(sizeof(int64_t) * (N ? N : 1));
+    uint32_t next_start = N ? start_index % N : 0;
+    int rc = ORA_OK;
+    for (uint32_t p = 0; p < n_pods && !rc; ++p) {
+        ora_labels pod;
+        memset(&pod, 0, sizeof pod);
+        const char *keys[3], *vals[3];
+        uint32_t k = 0;
+        if (memory && memory[p]) { keys[k] = "scv/memory"; vals[k++] = memory[p]; }
+        if (number && number[p]) { keys[k] = "scv/number"; vals[k++] = number[p]; }
+        if (clock && clock[p]) { keys[k] = "scv/clock"; vals[k++] = clock[p]; }
+        labels_set(&pod, k, keys, vals);
+        const uint32_t s0 = chain ? next_start : (N ? start_index % N : 0);
+        uint32_t nf = 0, visited = 0;
+        for (uint32_t i = 0; i < N && nf < want; ++i) { /* findNodesThatPassFilters */
+            const uint32_t n = (s0 + i) % N;
+            visited++;
+            if (yoda_filter(&pod, &cl->nodes[n])) found[nf++] = n;
+        }
+        next_start = N ? (s0 + visited) % N : 0;
+        start[p] = s0; sampled[p] = nf; processed[p] = visited;
+        lowest[p] = highest[p] = 0; top[p] = 0; ties[p] = 0; chosen[p] = -1;
+        if (nf == 1) { /* a single feasible node is taken without scoring */
+            chosen[p] = (int32_t)found[0];
+            ties[p] = 1;
+        } else if (nf > 1) {
+            ora_max mx;
+            collect_max_values(&pod, cl, 0, &mx);
+            for (uint32_t i = 0; i < nf && !rc; ++i) rc = yoda_score(&mx, &pod, &cl->nodes[found[i]], &list[i]);
+            if (!rc) {
+                int64_t hi = 0, lo = list[0];
+                for (uint32_t i = 0; i < nf; ++i) {
+                    if (list[i] < lo) lo = list[i];
+                    if (list[i] > hi) hi = list[i];
+                }
+                if (hi == lo) lo = (int64_t)((uint64_t)lo - 1);
+                lowest[p] = lo; highest[p] = hi;
+                ora_normalize_score(list, nf);
+                /* weight, other plugins, selectHost */
+                int64_t max_score = 0;
+                uint32_t cnt = 0;
+                for (uint32_t i = 0; i < nf; ++i) {
+                    const int64_t total = (int64_t)((uint64_t)list[i] * (uint64_t)weight + (uint64_t)(other ? other[found[i]] : 0));
+                    if (i == 0 || total > max_score) {
+                        max_score = total;
+                        chosen[p] = (int32_t)found[i];
+                        cnt = 1;
+                    } else if (total == max_score) {
+                        cnt++;
+                        if (tail_rand(seed, p, cnt) % cnt == 0) chosen[p] = (int32_t)found[i];
+                    }
+                }
+                top[p] = max_score; ties[p] = cnt;
+            }
+        }
+        labels_free(&pod);
+    }
+    free(found); free(list);
+    return rc;
+}

@@ -26,6 +26,11 @@ class Timing(C.Structure):
                 ("path", C.c_uint32), ("n_classes", C.c_uint32), ("n_groups", C.c_uint32)]
 
 
+class TailConfig(C.Structure):
+    _fields_ = [("weight", C.c_uint32), ("percentage", C.c_int32), ("seed", C.c_uint64), ("start_index", C.c_uint32), ("flags", C.c_uint32),
+                ("other_scores", C.c_void_p)]
+
+
 class Xchg(C.Structure):
     _fields_ = [("d_ptr", C.c_void_p), ("count", C.c_uint64), ("op", C.c_int32), ("reserved", C.c_int32)]
 
@@ -49,6 +54,8 @@ SYMBOLS = {
     "yoda_fetch_row": (_I, [_P, _U32, _I, _P, C.c_size_t]),
     "yoda_fetch_rows": (_I, [_P, _U32, _U32, _P, _P, _P]),
     "yoda_sync": (_I, [_P]),
+    "yoda_num_feasible_nodes_to_find": (_U32, [_U32, C.c_int32]),
+    "yoda_framework_tail": (_I, [_P, C.POINTER(TailConfig), _P, C.POINTER(_U32)]),
     "yoda_last_timing": (_I, [_P, C.POINTER(Timing)]),
     "yoda_result_matrices": (_I, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_U64)]),
     "yoda_result_raw_bytes": (_I, [_P, C.POINTER(_U32)]),

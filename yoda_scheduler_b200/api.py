@@ -12,6 +12,8 @@ from .snapshot import NODE_REC, POD_REQ, POD_RES, Snapshot
 
 EVAL_DECIDE, EVAL_FULL, EVAL_FORCE_DIRECT, EVAL_RAW32 = 0, 1, 2, 4
 ROW_FEASIBLE_BITS, ROW_RAW, ROW_NORM = 0, 1, 2
+TAIL_RES = np.dtype([("chosen", np.int32), ("sampled", np.uint32), ("processed", np.uint32), ("start", np.uint32), ("lowest", np.int64),
+                     ("highest", np.int64), ("top", np.int64), ("ties", np.uint32), ("reserved", np.uint32)])
 
 
 class Context:
@@ -134,6 +136,15 @@ class Context:
         sc, oc = C.c_uint32(), C.c_uint32()
         check(self.L.yoda_debug_pod_order(self.h, orig.ctypes.data, grp.ctypes.data, cls.ctypes.data, n_pods, C.byref(sc), C.byref(oc)))
         return orig, grp, cls, sc.value, oc.value
+
+    def framework_tail(self, n_pods: int, weight: int = 300, percentage: int = 0, seed: int = 0, start_index: int = 0, chain: bool = False, other=None):
+        """Sampling, weight and seeded selectHost over the last FULL batch (yoda_framework_tail).  Returns (results, next_start)."""
+        out = np.zeros(n_pods, TAIL_RES)
+        o = None if other is None else np.ascontiguousarray(other, dtype=np.int64)
+        cfg = _lib.TailConfig(weight, percentage, seed & (2**64 - 1), start_index, 1 if chain else 0, None if o is None else o.ctypes.data)
+        nxt = C.c_uint32()
+        check(self.L.yoda_framework_tail(self.h, C.byref(cfg), out.ctypes.data, C.byref(nxt)))
+        return out, nxt.value
 
     def normalize_scores(self, scores) -> np.ndarray:
         a = np.ascontiguousarray(scores, dtype=np.int64).copy()

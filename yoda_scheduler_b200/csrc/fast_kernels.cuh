@@ -684,14 +684,15 @@ __device__ __forceinline__ PodRegs pod_from_smem(const uint4 *sp, u32 i) {
 __device__ __forceinline__ void half_sync(int bar_id) { asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(HOT_THREADS) : "memory"); }
 
 #define SCORE_BLK 4  // chunk sizes stay multiples of this (hot_chunk in runtime.cu)
+template <bool DECIDE>
 struct ScoreSmem {
     uint4 sp[SCORE_CHUNK * 2];
     u32 m_s[SCORE_CHUNK];    // memory value of every pod of the chunk (ascending inside a run)
     u32 key_s[SCORE_CHUNK];  // run key: requirement group << 12 | class; a (group, class) run is contiguous in the sorted order
     __align__(16) u32 hi_s[HOT_WARPS][SCORE_CHUNK];
     __align__(16) u32 lo_s[HOT_WARPS][SCORE_CHUNK];
-    __align__(16) u32 cnt_s[HOT_WARPS][SCORE_CHUNK];   // DECIDE only: feasible nodes of the warp's slots
-    __align__(16) u32 best_s[HOT_WARPS][SCORE_CHUNK];  // DECIDE only: lowest node index holding the warp's top score
+    __align__(16) u32 cnt_s[DECIDE ? HOT_WARPS : 1][DECIDE ? SCORE_CHUNK : 4];   // DECIDE only: feasible nodes of the warp's slots
+    __align__(16) u32 best_s[DECIDE ? HOT_WARPS : 1][DECIDE ? SCORE_CHUNK : 4];  // DECIDE only: lowest node index holding the warp's top score
     u32 mark_s[HOT_WARPS][SCORE_CHUNK / 32];           // bit i: the warp's entry for pod i is set (it holds until the next set bit)
 };
 
@@ -706,7 +707,7 @@ struct ScoreSmem {
 // lowest-index node holding the top score, packed as (score << 32 | ~index) so that one 64-bit
 // atomicMax across the node tiles yields the choice -- no output pass is needed at all.
 template <int NPL, bool DECIDE>
-__device__ __forceinline__ void score_body(ScoreSmem &sm, int bar_id, u32 tid, u32 tile, u32 chunk, const DevSnap &s,
+__device__ __forceinline__ void score_body(ScoreSmem<DECIDE> &sm, int bar_id, u32 tid, u32 tile, u32 chunk, const DevSnap &s,
                                            const PodS *__restrict__ pods, u32 p_begin, u32 p_end, const u32 *__restrict__ tables,
                                            u64 *hilo, u64 *count, u64 *dkey, u32 chunk_pods) {
     const u32 lane = tid & 31, warp = tid >> 5;
@@ -991,7 +992,7 @@ template <int NPL, bool DECIDE>
 __global__ void __launch_bounds__(HOT_THREADS, SCORE_MINB) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
                                                             const u32 *__restrict__ tables, u64 *hilo, u64 *count, u64 *dkey,
                                                             u32 chunk_pods) {  // pods per CTA: a multiple of SCORE_BLK, <= SCORE_CHUNK
-    __shared__ ScoreSmem sm;
+    __shared__ ScoreSmem<DECIDE> sm;
     score_body<NPL, DECIDE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo, count, dkey, chunk_pods);
 }
 

@@ -18,6 +18,7 @@
 #include "direct_kernels.cuh"
 #include "fast_kernels.cuh"
 #include "seq_kernels.cuh"
+#include "tail_kernels.cuh"
 
 // ------------------------------------------------------------------------------------------
 // errors
@@ -139,6 +140,13 @@ struct yoda_ctx {
     // NormalizeScore list scratch
     i64 *d_list = nullptr, *d_lohi = nullptr;
     u32 list_cap = 0;
+    // framework tail scratch (yoda_framework_tail)
+    u32 *tl_tilecnt = nullptr;
+    size_t tl_tilecnt_cap = 0;
+    TailOut *tl_out = nullptr;
+    u32 tl_out_cap = 0;
+    i64 *tl_other = nullptr;
+    u32 tl_other_cap = 0;
     // pinned staging of yoda_fetch_rows / yoda_fetch_row (uint32 score rows are widened from here)
     u8 *h_rows = nullptr;
     size_t h_rows_cap = 0;
@@ -320,6 +328,7 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     dev_free(c->ord_keys_out); dev_free(c->ord_iota);
     if (c->ord_tmp) cudaFree(c->ord_tmp);
     dev_free(c->d_wide_list); dev_free(c->d_wide_cnt);
+    dev_free(c->tl_tilecnt); dev_free(c->tl_out); dev_free(c->tl_other);
     dev_free(c->d_wide_flag); dev_free(c->d_lohi); dev_free(c->d_list); dev_free(c->d_upd);
     dev_free(c->d_req); dev_free(c->d_pods); dev_free(c->d_max6); dev_free(c->d_count);
     dev_free(c->d_hilo); dev_free(c->d_ckey); dev_free(c->d_res);
@@ -1315,6 +1324,87 @@ extern "C" int yoda_result_raw_bytes(yoda_ctx *c, uint32_t *bytes) {
     std::lock_guard<std::mutex> lk(c->mu);
     if (!c->last_full) return fail(YODA_E_STATE, "no YODA_EVAL_FULL result");
     *bytes = c->res_raw32 ? 4u : 8u;
+    return YODA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// framework tail (tail_kernels.cuh): sampling, weight, seeded selectHost over the last FULL result
+// ------------------------------------------------------------------------------------------
+extern "C" uint32_t yoda_num_feasible_nodes_to_find(uint32_t num_all_nodes, int32_t percentage) {
+    // [3P] k8s v1.20.0 generic_scheduler.go numFeasibleNodesToFind: minFeasibleNodesToFind 100, minimum percentage 5,
+    // adaptive percentage 50 - nodes/125 when the configured one is <= 0 (deploy/yoda-scheduler.yaml:18 sets 0)
+    const int32_t all = (int32_t)std::min<uint32_t>(num_all_nodes, 0x7FFFFFFFu);
+    if (all < 100 || percentage >= 100) return num_all_nodes;
+    int32_t adaptive = percentage;
+    if (adaptive <= 0) adaptive = std::max(5, 50 - all / 125);
+    const int32_t num = (int32_t)((int64_t)all * adaptive / 100);
+    return num < 100 ? 100u : (uint32_t)num;
+}
+
+extern "C" int yoda_framework_tail(yoda_ctx *c, const yoda_tail_config *cfg, yoda_tail_result *out, uint32_t *next_start) {
+    static_assert(sizeof(TailOut) == sizeof(yoda_tail_result), "TailOut mirrors yoda_tail_result");
+    if (!c || !cfg || !out) return fail(YODA_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard dg(c->cfg.device);
+    if (!c->last_full || c->last_P == 0) return fail(YODA_E_STATE, "yoda_framework_tail works on the matrices of a YODA_EVAL_FULL batch: none is held");
+    if (c->comm || c->cfg.shard_count != 1) return fail(YODA_E_STATE, "yoda_framework_tail is not available on a node-sharded context");
+    if (cfg->flags & ~YODA_TAIL_CHAIN) return fail(YODA_E_ARG, "unknown tail flags 0x%x", cfg->flags);
+    const u32 P = c->last_P, N = c->snap.n_nodes;
+    cudaStream_t st = c->stream;
+    if (N == 0) {
+        for (u32 p = 0; p < P; ++p) {
+            memset(&out[p], 0, sizeof out[p]);
+            out[p].chosen = -1;
+        }
+        if (next_start) *next_start = 0;
+        return YODA_OK;
+    }
+    const u32 tiles = (u32)(c->stride / TAIL_TILE);
+    const u64 words = c->stride / 32;
+    if ((size_t)P * tiles > c->tl_tilecnt_cap) {
+        CU(cudaStreamSynchronize(st));
+        dev_free(c->tl_tilecnt);
+        c->tl_tilecnt_cap = 0;
+        TRY(dev_alloc(&c->tl_tilecnt, (size_t)P * tiles));
+        c->tl_tilecnt_cap = (size_t)P * tiles;
+    }
+    if (P > c->tl_out_cap) {
+        CU(cudaStreamSynchronize(st));
+        dev_free(c->tl_out);
+        c->tl_out_cap = 0;
+        TRY(dev_alloc(&c->tl_out, P));
+        c->tl_out_cap = P;
+    }
+    const i64 *d_other = nullptr;
+    if (cfg->other_scores) {
+        if (N > c->tl_other_cap) {
+            CU(cudaStreamSynchronize(st));
+            dev_free(c->tl_other);
+            c->tl_other_cap = 0;
+            TRY(dev_alloc(&c->tl_other, c->snap.cap));
+            c->tl_other_cap = c->snap.cap;
+        }
+        CU(cudaMemcpyAsync(c->tl_other, cfg->other_scores, (size_t)N * sizeof(i64), cudaMemcpyHostToDevice, st));
+        d_other = c->tl_other;
+    }
+    const u32 want = yoda_num_feasible_nodes_to_find(N, cfg->percentage);
+    const int chain = (cfg->flags & YODA_TAIL_CHAIN) ? 1 : 0;
+    const u64 cells = (u64)P * tiles;
+    k_tail_tilecnt<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(c->d_bits, words, P, tiles, c->tl_tilecnt);
+    CU(cudaGetLastError());
+    if (chain)
+        k_tail_window<<<1, 32, 0, st>>>(c->d_bits, words, c->tl_tilecnt, tiles, P, N, want, cfg->start_index, 1, c->tl_out);
+    else
+        k_tail_window<<<(P + 7) / 8, 256, 0, st>>>(c->d_bits, words, c->tl_tilecnt, tiles, P, N, want, cfg->start_index, 0, c->tl_out);
+    CU(cudaGetLastError());
+    if (c->res_raw32)
+        k_tail_pick<true><<<(P + 7) / 8, 256, 0, st>>>(c->d_bits, words, c->d_raw, c->stride, P, N, cfg->weight, cfg->seed, d_other, c->snap.node_base, c->tl_out);
+    else
+        k_tail_pick<false><<<(P + 7) / 8, 256, 0, st>>>(c->d_bits, words, c->d_raw, c->stride, P, N, cfg->weight, cfg->seed, d_other, c->snap.node_base, c->tl_out);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(out, c->tl_out, (size_t)P * sizeof(TailOut), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (next_start) *next_start = chain ? (out[P - 1].start + out[P - 1].processed) % N : cfg->start_index % N;
     return YODA_OK;
 }
 
