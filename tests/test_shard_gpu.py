@@ -6,6 +6,7 @@ import sys
 import numpy as np
 import pytest
 
+from oracle import oracle as ora
 from parity import assert_matches_oracle
 from yoda_scheduler_b200 import api, shard, synth
 
@@ -119,8 +120,22 @@ def _nccl_worker_body(rank, world, port, N, P, out_dir):
         _widen(snap, 0)
         ctx.load_snapshot(snap)
     mixed = ctx.eval(reqs, api.EVAL_DECIDE)
-    assert ctx.timing().path == (0 if rank == 1 else 1)
+    assert ctx.timing().path == 1      # a wide node no longer costs its shard the table path
     np.save(os.path.join(out_dir, f"mix{rank}.npy"), mixed)
+    mixed_full = ctx.eval(reqs, api.EVAL_FULL)
+    assert np.array_equal(mixed_full, mixed)
+    # FULL with a class table that does not fit the packed format on ONE shard (a 4e9 clock: Clock*100/MaxBandwidth leaves
+    # 21 bits): that shard's kernels switch to the exact path on the device (no host round trip), the other shard's do not
+    snap = synth.make_snapshot(per, node_offset=rank * per)
+    if rank == 1:
+        node = int(np.nonzero((snap.has_scv == 1) & (snap.n_cards == 8))[0][5])
+        snap.clock[node, :] = np.uint64(4_000_000_000)
+    ctx.load_snapshot(snap)
+    over = ctx.eval(reqs, api.EVAL_FULL)
+    assert ctx.timing().path == (0 if rank == 1 else 1), ctx.timing().path
+    np.save(os.path.join(out_dir, f"over{rank}.npy"), over)
+    np.save(os.path.join(out_dir, f"over_raw{rank}.npy"), np.stack([ctx.fetch_row(p, api.ROW_RAW, per) for p in range(40)]))
+    np.save(os.path.join(out_dir, f"over_norm{rank}.npy"), np.stack([ctx.fetch_row(p, api.ROW_NORM, per) for p in range(40)]))
     dist.barrier()
     ctx.close()
     dist.destroy_process_group()
@@ -144,11 +159,23 @@ def test_two_gpus_nccl(tmp_path):
         _widen(snap, N // world)
         single.load_snapshot(snap)
         want_mix = single.eval(reqs, api.EVAL_DECIDE)
-        assert single.timing().path == 0
+        assert single.timing().path == 1
+        snap = synth.make_snapshot(N)
+        node = N // world + int(np.nonzero((snap.has_scv[N // world:] == 1) & (snap.n_cards[N // world:] == 8))[0][5])
+        snap.clock[node, :] = np.uint64(4_000_000_000)
+        single.load_snapshot(snap)
+        want_over = single.eval(reqs, api.EVAL_FULL | api.EVAL_FORCE_DIRECT)
+        want_raw = np.stack([single.fetch_row(p, api.ROW_RAW, N) for p in range(40)])
+        want_norm = np.stack([single.fetch_row(p, api.ROW_NORM, N) for p in range(40)])
+    o = ora.OracleCluster.from_snapshot(snap).eval(synth.make_pod_labels(P, 31), threads=8, full=False)
+    assert np.array_equal(want_over["chosen"], o["chosen"]) and np.array_equal(want_over["highest"], o["highest"])
     for r in range(world):
         assert np.array_equal(np.load(tmp_path / f"res{r}.npy"), want)
         assert np.array_equal(np.load(tmp_path / f"dec{r}.npy"), want)
         assert np.array_equal(np.load(tmp_path / f"mix{r}.npy"), want_mix)
+        assert np.array_equal(np.load(tmp_path / f"over{r}.npy"), want_over)
+    assert np.array_equal(np.concatenate([np.load(tmp_path / f"over_raw{r}.npy") for r in range(world)], axis=1), want_raw)
+    assert np.array_equal(np.concatenate([np.load(tmp_path / f"over_norm{r}.npy") for r in range(world)], axis=1), want_norm)
 
 
 def test_pod_sharding_equals_single():

@@ -267,7 +267,21 @@ __device__ __forceinline__ void dev_lo_hi(const u64 *hilo, u32 p, i64 &lo, i64 &
 }
 
 // Output side of the thread = pod kernel (MODE 2): where the verdicts and scores of the listed nodes go.
+// Device-side path selection (node-sharded FULL batches): whether a shard's class tables fit the packed format is known
+// on the device only (FastCtl::err); instead of a host round trip both paths are launched and each kernel looks at the
+// word: GATE_IF_ZERO kernels (table path, wide-node list) run when it is 0, GATE_IF_SET kernels (exact path) otherwise.
+#define GATE_NONE 0
+#define GATE_IF_ZERO 1
+#define GATE_IF_SET 2
+__device__ __forceinline__ bool gate_closed(const u32 *gate, int mode) {
+    if (mode == GATE_NONE) return false;
+    const bool set = *reinterpret_cast<const volatile u32 *>(gate) != 0;
+    return mode == GATE_IF_ZERO ? set : !set;
+}
+
 struct DirectOut {
+    const u32 *gate;  // see gate_closed
+    int gate_mode;
     u64 *count, *ckey;
     i64 *raw;    // FULL mode: result matrices (null otherwise); entries of the listed nodes are overwritten
     u8 *norm;
@@ -284,6 +298,7 @@ template <int MODE>
 __global__ void __launch_bounds__(DPT) k_direct_pods(DevSnap s, const PodC *__restrict__ pods, u32 P, u32 nodes_per_cta,
                                                      u64 *max6, u64 *hilo, const u32 *__restrict__ node_list, u32 n_list, DirectOut out) {
     __shared__ DirectTile sm;
+    if (gate_closed(out.gate, out.gate_mode)) return;
     const u32 p = blockIdx.x * DPT + threadIdx.x;
     const bool active = p < P;
     PodC pod;
@@ -406,7 +421,8 @@ template <bool WRITE>
 __global__ void __launch_bounds__(DCT) k_direct_out(DevSnap s, const PodC *__restrict__ pods, u32 P, u32 pods_per_cta,
                                                     const u64 *__restrict__ max6, u64 *count,
                                                     const u64 *__restrict__ hilo, u64 *ckey, i64 *raw_out, u8 *norm_out,
-                                                    u32 *bits_out, u64 stride) {
+                                                    u32 *bits_out, u64 stride, const u32 *gate, int gate_mode) {
+    if (gate_closed(gate, gate_mode)) return;
     const u32 n = blockIdx.x * DCT + threadIdx.x;
     const bool live = n < s.n_nodes;
     u64 fr[G], tot[G], ck[G], co[G], bw[G], pw[G];

@@ -991,16 +991,20 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
 template <int NPL, bool DECIDE>
 __global__ void __launch_bounds__(HOT_THREADS, SCORE_MINB) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
                                                             const u32 *__restrict__ tables, u64 *hilo, u64 *count, u64 *dkey,
-                                                            u32 chunk_pods) {  // pods per CTA: a multiple of SCORE_BLK, <= SCORE_CHUNK
+                                                            u32 chunk_pods,  // pods per CTA: a multiple of SCORE_BLK, <= SCORE_CHUNK
+                                                            const u32 *gate) {  // non-null: run only while *gate == 0 (see gate_closed)
     __shared__ ScoreSmem<DECIDE> sm;
+    if (gate_closed(gate, gate ? GATE_IF_ZERO : GATE_NONE)) return;
     score_body<NPL, DECIDE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo, count, dkey, chunk_pods);
 }
 
 template <int NPL, bool WRITE, bool RAW32>
 __global__ void __launch_bounds__(HOT_THREADS, 2) k_fast_out(DevSnap s, const PodS *__restrict__ pods, const u64 *__restrict__ hilo,
                                                              u32 p_begin, u32 p_end, const u32 *__restrict__ tables, u64 *count, u64 *ckey,
-                                                             i64 *raw_out, u8 *norm_out, u32 *bits_out, u64 stride, u32 chunk_pods) {
+                                                             i64 *raw_out, u8 *norm_out, u32 *bits_out, u64 stride, u32 chunk_pods,
+                                                             const u32 *gate) {  // non-null: run only while *gate == 0
     __shared__ OutSmem sm;
+    if (gate_closed(gate, gate ? GATE_IF_ZERO : GATE_NONE)) return;
     out_body<NPL, WRITE, RAW32>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, hilo, p_begin, p_end, tables, count, ckey, raw_out, norm_out,
                          bits_out, stride, chunk_pods);
 }

@@ -91,7 +91,7 @@ static int nccl_load() {
 enum { EV_START = 0, EV_PREP, EV_MAX, EV_SCORE, EV_WRITE, EV_H2D0, EV_H2D1, EV_D2H0, EV_D2H1, EV_COUNT };
 
 #ifndef SCORE_NPL
-#define SCORE_NPL 4  // nodes per lane in the score pass (its per-node state is 7 registers)
+#define SCORE_NPL 2  // nodes per lane in the score pass: 2 measured best on B200 (c3 0.98 ms vs 1.04 at 4, 1.21 at 1; same order at 125k x 10k and 50k x 10k)
 #endif
 
 struct yoda_ctx {
@@ -171,6 +171,9 @@ struct yoda_ctx {
     FastCtl *fw_ctl = nullptr, *fw_hctl = nullptr;
     u32 fw_n_groups = 0, fw_n_classes = 0;
     bool fw_small = false, fw_allow_defer = false, fw_deferred_err = false;
+    bool fw_defer_groups = false;  // the group count stays on the device until the class count is read back
+    bool fw_gate_ok = false;       // node-sharded FULL batch: fast/exact path selected on the device by FastCtl::err ...
+    bool fw_gated = false;         // ... and this evaluation is running that way (both paths launched, see gate_closed)
     bool fw_decide_merged = false;
     bool fw_groups_pending = false;  // the group count (and its capacity check) has not been read back yet
     // sequential-commit scratch
@@ -632,7 +635,7 @@ static int fast_read_ctl(yoda_ctx *c) {
 }
 
 // ---- direct path bodies ---------------------------------------------------------------------
-static int direct_pods_launch(yoda_ctx *c, int mode) {
+static int direct_pods_launch(yoda_ctx *c, int mode, bool gated = false) {
     const u32 P = c->ph_P, N = c->snap.n_nodes;
     if (!N) return YODA_OK;
     const u32 gx = (P + DPT - 1) / DPT;
@@ -640,7 +643,11 @@ static int direct_pods_launch(yoda_ctx *c, int mode) {
     chunks = std::min(chunks, 65535u);
     const u32 npc = round_up((N + chunks - 1) / chunks, DTN);
     dim3 grid(gx, (N + npc - 1) / npc);
-    const DirectOut none{};
+    DirectOut none{};
+    if (gated) {
+        none.gate = &c->fw_ctl->err;
+        none.gate_mode = GATE_IF_SET;
+    }
     if (mode == 0)
         k_direct_pods<0><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo, nullptr, 0, none);
     else
@@ -660,6 +667,10 @@ static int wide_pods_launch(yoda_ctx *c, int mode) {
     const u32 npc = round_up((W + chunks - 1) / chunks, DTN);
     dim3 grid(gx, (W + npc - 1) / npc);
     DirectOut out{};
+    if (c->fw_gated) {
+        out.gate = &c->fw_ctl->err;
+        out.gate_mode = GATE_IF_ZERO;
+    }
     if (mode == 0) {
         k_direct_pods<0><<<grid, DPT, 0, c->stream>>>(c->snap, c->d_pods, P, npc, c->d_max6, c->d_hilo, c->d_wide_list, W, out);
     } else if (mode == 1) {
@@ -683,7 +694,7 @@ static int wide_pods_launch(yoda_ctx *c, int mode) {
     return YODA_OK;
 }
 
-static int direct_out_launch(yoda_ctx *c) {
+static int direct_out_launch(yoda_ctx *c, bool gated = false) {
     const u32 P = c->ph_P, N = c->snap.n_nodes;
     if (!N) return YODA_OK;
     cudaStream_t st = c->stream;
@@ -691,19 +702,21 @@ static int direct_out_launch(yoda_ctx *c) {
     const u32 gx = (N + DCT - 1) / DCT;
     const u32 want_y = std::max(1u, 2368u / gx);
     u32 ppc = std::max(1u, (P + want_y - 1) / want_y);
-    ppc = std::min(ppc, 64u);
+    if (!gated) ppc = std::min(ppc, 64u);  // (a gated launch usually finds its gate closed: one wave of CTAs, not thousands)
     ppc = std::max(ppc, (P + 65534u) / 65535u);
     dim3 grid(gx, (P + ppc - 1) / ppc);
-    if (full) {
+    if (full && !gated) {
         TRY(ensure_raw(c, (size_t)P * c->stride * sizeof(i64)));  // a YODA_EVAL_RAW32 batch that fell back to these kernels
         c->res_raw32 = false;
     }
+    const u32 *gate = gated ? &c->fw_ctl->err : nullptr;
+    const int gm = gated ? GATE_IF_SET : GATE_NONE;
     if (full)
         k_direct_out<true><<<grid, DCT, 0, st>>>(c->snap, c->d_pods, P, ppc, c->d_max6, c->d_count, c->d_hilo, c->d_ckey, c->d_raw,
-                                                 c->d_norm, c->d_bits, c->stride);
+                                                 c->d_norm, c->d_bits, c->stride, gate, gm);
     else
         k_direct_out<false><<<grid, DCT, 0, st>>>(c->snap, c->d_pods, P, ppc, c->d_max6, c->d_count, c->d_hilo, c->d_ckey, nullptr,
-                                                  nullptr, nullptr, c->stride);
+                                                  nullptr, nullptr, c->stride, gate, gm);
     LAUNCHED(c);
     return YODA_OK;
 }
@@ -749,7 +762,7 @@ static int fast_phase0(yoda_ctx *c) {
     // On one GPU the group count stays on the device until the class count is read back (fast_classes):
     // the kernels below take it from ctl.  Sharded / phase-split evaluations read it now, because the
     // maxima are exchanged right after this phase and a fallback decided later could not undo that.
-    const bool count_on_device = c->fw_allow_defer;
+    const bool count_on_device = c->fw_defer_groups;
     u32 groups_bound = std::min(P, FAST_GROUP_CAP);
     if (!count_on_device) {
         TRY(fast_read_ctl(c));
@@ -801,12 +814,13 @@ static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     const u32 chunk = hot_chunk(p_end - p_begin, tiles, c->score_slots, SCORE_CHUNK);
     c->last_score_chunk = chunk;
     const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
+    const u32 *gate = c->fw_gated ? &c->fw_ctl->err : nullptr;
     if (c->fw_decide_merged)
         k_fast_score<SCORE_NPL, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
-                                                                           c->d_count, c->d_ckey, chunk);
+                                                                           c->d_count, c->d_ckey, chunk, gate);
     else
         k_fast_score<SCORE_NPL, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
-                                                                            c->d_count, c->d_ckey, chunk);
+                                                                            c->d_count, c->d_ckey, chunk, gate);
     LAUNCHED(c);
     return YODA_OK;
 }
@@ -819,19 +833,22 @@ static int fast_out_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     c->last_out_chunk = chunk;
     const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
     const bool full = (c->ph_flags & YODA_EVAL_FULL) != 0;
+    const u32 *gate = c->fw_gated ? &c->fw_ctl->err : nullptr;
     if (full) c->res_raw32 = (c->ph_flags & YODA_EVAL_RAW32) != 0 && c->narrow_ok;  // a wide node's Score may not fit 32 bits
     if (full && c->res_raw32)
         k_fast_out<4, true, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
-                                                                       c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride, chunk);
+                                                                       c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride, chunk, gate);
     else if (full)
         k_fast_out<4, true, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
-                                                                        c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride, chunk);
+                                                                        c->d_ckey, c->d_raw, c->d_norm, c->d_bits, c->stride, chunk, gate);
     else
         k_fast_out<4, false, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, c->d_hilo, p_begin, p_end, c->fw_tables, c->d_count,
-                                                                  c->d_ckey, nullptr, nullptr, nullptr, c->stride, chunk);
+                                                                  c->d_ckey, nullptr, nullptr, nullptr, c->stride, chunk, gate);
     LAUNCHED(c);
     return YODA_OK;
 }
+
+static int exchange_locked(yoda_ctx *c, int phase);
 
 // classes -> tables.  Returns with ph_path = 0 if the batch cannot use the tables.
 static int fast_classes(yoda_ctx *c) {
@@ -859,6 +876,10 @@ static int fast_classes(yoda_ctx *c) {
             c->fw_deferred_err = true;  // checked once at the end of the evaluation instead of stalling here
             return YODA_OK;
         }
+        if (c->fw_gate_ok) {
+            c->fw_gated = true;  // both paths are launched, the device picks (gate_closed)
+            return YODA_OK;
+        }
         TRY(fast_read_ctl(c));
         if (c->fw_hctl->err) c->ph_path = 0;
         return YODA_OK;
@@ -881,6 +902,9 @@ static int fast_classes(yoda_ctx *c) {
             k_init_partials<<<(P + 255) / 256, 256, 0, st>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, P);
             LAUNCHED(c);
             TRY(direct_pods_launch(c, 0));
+            // node-sharded: the maxima exchanged after phase 0 are void as well; every shard is here (the group count
+            // depends on the pods alone), so they all repeat the exchange
+            TRY(exchange_locked(c, 0));
             return YODA_OK;
         }
     }
@@ -902,6 +926,10 @@ static int fast_classes(yoda_ctx *c) {
     }
     if (c->fw_allow_defer) {
         c->fw_deferred_err = true;  // "every class fits the packed table": read back with the results
+        return YODA_OK;
+    }
+    if (c->fw_gate_ok) {
+        c->fw_gated = true;  // both paths are launched, the device picks (gate_closed); the verdict is read back with the results
         return YODA_OK;
     }
     TRY(fast_read_ctl(c));
@@ -952,6 +980,7 @@ static int phase1(yoda_ctx *c) {
     if (c->ph_path == 1) {
         TRY(fast_score_launch(c, 0, c->ph_P));
         TRY(wide_pods_launch(c, 1));
+        if (c->fw_gated) TRY(direct_pods_launch(c, 1, true));
     }
     if (c->ph_path == 0) TRY(direct_pods_launch(c, 1));
     CU(cudaEventRecord(c->ev[EV_SCORE], c->stream));
@@ -963,7 +992,9 @@ static int phase2(yoda_ctx *c) {
     if (c->ph_path == 1 && c->fw_decide_merged) return wide_pods_launch(c, 2);  // phase 1 already produced the table nodes' counts and choices
     if (c->ph_path == 1) {
         TRY(fast_out_launch(c, 0, c->ph_P));
-        return wide_pods_launch(c, 2);  // overwrites the wide nodes' matrix entries
+        TRY(wide_pods_launch(c, 2));  // overwrites the wide nodes' matrix entries
+        if (c->fw_gated) TRY(direct_out_launch(c, true));
+        return YODA_OK;
     }
     return direct_out_launch(c);
 }
@@ -985,11 +1016,15 @@ static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
     c->stride = round_up(std::max(c->snap.n_nodes, 1u), 1024);  // rows padded to the hot kernels' CTA tile
     if (flags & ~(YODA_EVAL_FULL | YODA_EVAL_FORCE_DIRECT | YODA_EVAL_RAW32)) return fail(YODA_E_ARG, "unknown evaluation flags 0x%x", flags);
     c->ph_path = (c->table_ok && !(flags & YODA_EVAL_FORCE_DIRECT)) ? 1 : 0;
-    if (flags & YODA_EVAL_FULL) TRY(ensure_matrices(c, P, c->stride, (c->ph_path == 1 && c->narrow_ok && (flags & YODA_EVAL_RAW32)) ? 4u : 8u));
+    // (a node-sharded FULL batch may pick the exact kernels on the device: room for int64 rows either way)
+    if (flags & YODA_EVAL_FULL) TRY(ensure_matrices(c, P, c->stride, (c->ph_path == 1 && c->narrow_ok && (flags & YODA_EVAL_RAW32) && !c->comm) ? 4u : 8u));
     if (c->ph_path == 1) TRY(ensure_fast(c, P));
     c->ph_P = P;
     c->ph_flags = flags;
     c->fw_groups_pending = false;
+    c->fw_gated = false;
+    c->fw_gate_ok = false;
+    c->fw_defer_groups = false;
     c->ph_done = -1;
     c->last_P = 0;
     c->last_full = false;
@@ -1039,6 +1074,8 @@ static void collect_timing(yoda_ctx *c, bool copies) {
 
 static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
     c->fw_allow_defer = (c->comm == nullptr);
+    c->fw_defer_groups = true;
+    c->fw_gate_ok = (c->comm != nullptr) && (c->ph_flags & YODA_EVAL_FULL);
     c->fw_deferred_err = false;
     c->fw_decide_merged = (c->comm == nullptr) && !(c->ph_flags & YODA_EVAL_FULL) && c->ph_path == 1;
     c->fw_agree = (c->comm != nullptr) && !(c->ph_flags & YODA_EVAL_FULL);
@@ -1050,6 +1087,8 @@ static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
     TRY(exchange_locked(c, 2));
     TRY(phase3(c));
     c->fw_allow_defer = false;
+    c->fw_defer_groups = false;
+    c->fw_gate_ok = false;
     c->fw_agree = false;
     c->ph_done = 3;
     c->last_P = c->ph_P;
@@ -1071,6 +1110,16 @@ static int redo_direct_if_flagged(yoda_ctx *c, const yoda_pod_req *d_req, u32 er
     return YODA_OK;
 }
 
+// A gated evaluation (see gate_closed) learns only now which kernels did the work: fw_hctl holds the verdict.
+static void gate_verdict(yoda_ctx *c) {
+    if (!c->fw_gated) return;
+    c->fw_gated = false;
+    if (c->fw_hctl->err) {  // the exact kernels: int64 rows
+        c->ph_path = 0;
+        c->res_raw32 = false;
+    }
+}
+
 #define STAGE_PODS 4096u  // batches up to this size go through the library's pinned staging buffers
 extern "C" int yoda_eval_batch(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32 flags, yoda_pod_result *out) {
     if (!c || (P && (!pods || !out))) return fail(YODA_E_ARG, "null argument");
@@ -1090,8 +1139,9 @@ extern "C" int yoda_eval_batch(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32
     CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
     CU(cudaEventRecord(c->ev[EV_D2H1], st));
     const bool deferred = c->fw_deferred_err;
-    if (deferred) CU(cudaMemcpyAsync(c->fw_hctl, c->fw_ctl, sizeof(FastCtl), cudaMemcpyDeviceToHost, st));
+    if (deferred || c->fw_gated) CU(cudaMemcpyAsync(c->fw_hctl, c->fw_ctl, sizeof(FastCtl), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    gate_verdict(c);
     if (deferred && c->fw_hctl->err) {
         TRY(redo_direct_if_flagged(c, c->d_req, c->fw_hctl->err));
         CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
@@ -1110,6 +1160,10 @@ extern "C" int yoda_eval_batch_device(yoda_ctx *c, const void *d_pods, u32 P, u3
     if (P == 0) return YODA_OK;
     TRY(begin_locked(c, P, flags));
     TRY(run_all_locked(c, (const yoda_pod_req *)d_pods));
+    if (c->fw_gated) {
+        TRY(fast_read_ctl(c));
+        gate_verdict(c);
+    }
     if (c->fw_deferred_err) {
         TRY(fast_read_ctl(c));
         TRY(redo_direct_if_flagged(c, (const yoda_pod_req *)d_pods, c->fw_hctl->err));
