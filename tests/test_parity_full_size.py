@@ -38,7 +38,8 @@ def _boundary_pods(orig, grp, cls, score_chunk, out_chunk, cap):
     pos = set()
     for chunk in (score_chunk, out_chunk):
         for c0 in range(0, P, chunk):
-            pos.update((c0, min(P, c0 + chunk) - 1))
+            c1 = min(P, c0 + chunk)
+            pos.update((c0, min(c0 + 1, c1 - 1), max(c1 - 2, c0), c1 - 1))
     g_change = np.nonzero(grp[1:] != grp[:-1])[0] + 1
     pos.update(g_change.tolist())
     pos.update((g_change - 1).tolist())
@@ -47,6 +48,8 @@ def _boundary_pods(orig, grp, cls, score_chunk, out_chunk, cap):
     if len(c_change) > 400:
         c_change = rng.choice(c_change, 400, replace=False)
     pos.update(c_change.tolist())
+    if len(pos) < 2200:     # whatever chunk sizes the runtime picked: never fewer than 2200 pods, the rest drawn at random
+        pos.update(rng.choice(P, 2200 - len(pos), replace=False).tolist())
     pos = sorted(pos)
     if len(pos) > cap:
         pos = sorted(rng.choice(pos, cap, replace=False).tolist())

@@ -8,6 +8,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <shared_mutex>
 #include <stdexcept>
 #include <string>
 #include <unordered_map>
@@ -55,11 +56,13 @@ inline Status NewStatus(Code c, std::string msg = "") { return Status{c, std::mo
 struct StateData {
     virtual ~StateData() = default;
 };
-// framework.CycleState: per-scheduling-cycle key/value store with its own lock
+// framework.CycleState: per-scheduling-cycle key/value store with its own read/write lock (Go: sync.RWMutex)
 class CycleState {
    public:
     void Lock() { mu_.lock(); }
     void Unlock() { mu_.unlock(); }
+    void RLock() { mu_.lock_shared(); }
+    void RUnlock() { mu_.unlock_shared(); }
     void Write(const std::string &key, std::shared_ptr<StateData> v) { data_[key] = std::move(v); }
     std::shared_ptr<StateData> Read(const std::string &key) const {  // nullptr == "not found" error
         auto it = data_.find(key);
@@ -67,7 +70,7 @@ class CycleState {
     }
 
    private:
-    std::mutex mu_;
+    std::shared_mutex mu_;
     std::unordered_map<std::string, std::shared_ptr<StateData>> data_;
 };
 

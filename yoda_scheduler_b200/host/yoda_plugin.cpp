@@ -183,8 +183,12 @@ static const char *kMemoKey = "yoda/b200";
 // First plugin call of a cycle evaluates the pod against every node once (one device pass) and
 // stores the rows in CycleState under the state lock, as collection.go:53-55 does for "Max".
 std::shared_ptr<Yoda::Memo> Yoda::memo(framework::CycleState &state, const v1::Pod &pod, Status *st) {
-    state.Lock();
+    state.RLock();  // every call after the first of a cycle: a shared read, 16 framework threads at once
     auto have = std::dynamic_pointer_cast<Memo>(state.Read(kMemoKey));
+    state.RUnlock();
+    if (have) return have;
+    state.Lock();
+    have = std::dynamic_pointer_cast<Memo>(state.Read(kMemoKey));
     if (!have) {
         std::unique_lock<std::shared_mutex> lk(mu_);
         Status s = sync_locked();
@@ -266,9 +270,9 @@ std::pair<int64_t, Status> Yoda::Score(framework::CycleState &state, const v1::P
     const int32_t idx = NodeIndex(nodeName);
     if (!m->known(idx))  // :117-122; a node registered after the cycle's evaluation is not part of it either
         return {0, NewStatus(framework::Error, "Score Node Error: Scv.core.run-linux.com \"" + nodeName + "\" not found")};
-    state.Lock();
+    state.RLock();
     const bool have_max = std::dynamic_pointer_cast<Data>(state.Read("Max")) != nullptr;
-    state.Unlock();
+    state.RUnlock();
     if (!have_max)  // algorithm.go:29-37: "Max" must have been written
         return {0, NewStatus(framework::Error, "Score Node Error: not found")};
     return {m->raw[idx], NewStatus(framework::Success, "")};
@@ -279,9 +283,9 @@ std::pair<int64_t, Status> Yoda::Score(framework::CycleState &state, const v1::P
 // the list is rescaled on the device as given.  Panics (throws) on an empty list like the Go code.
 Status Yoda::NormalizeScore(framework::CycleState &state, const v1::Pod &pod, framework::NodeScoreList &scores) {
     if (scores.empty()) throw std::out_of_range("index out of range [0] with length 0");  // scores[0], :135
-    state.Lock();
+    state.RLock();
     auto m = std::dynamic_pointer_cast<Memo>(state.Read(kMemoKey));
-    state.Unlock();
+    state.RUnlock();
     bool own = m && scores.size() == m->res.feasible;
     std::vector<int32_t> idx(scores.size(), -1);
     for (size_t i = 0; own && i < scores.size(); ++i) {
