@@ -549,7 +549,8 @@ __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__r
 #define HOT_WARPS (HOT_THREADS / 32)
 #define HOT_CHUNK 128  // pods per CTA of the output pass
 #ifndef SCORE_CHUNK
-#define SCORE_CHUNK 256  // pods per CTA of the score pass: every chunk starts with a full evaluation of the CTA's nodes
+#define SCORE_CHUNK 192  // pods per CTA of the score pass: every chunk starts with a full evaluation of the CTA's nodes
+                         // (192 keeps the CTA's shared memory near 52 KB: four CTAs per SM; measured best of 128/192/256)
 #endif
 
 template <int NPL>
@@ -684,8 +685,13 @@ __device__ __forceinline__ PodRegs pod_from_smem(const uint4 *sp, u32 i) {
 __device__ __forceinline__ void half_sync(int bar_id) { asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(HOT_THREADS) : "memory"); }
 
 #define SCORE_BLK 4  // chunk sizes stay multiples of this (hot_chunk in runtime.cu)
-template <bool DECIDE>
+template <int NPL, bool DECIDE>
 struct ScoreSmem {
+    // the CTA's nodes, resident for the whole chunk: FreeMemory of the eight card slots, and the card contributions of the
+    // current (group, class) run with the group's clock tests folded in (as hot_load_class does for the output pass);
+    // [half][node]: consecutive lanes read consecutive 16-byte pieces
+    uint4 fr[2][HOT_WARPS * NPL * 32];
+    uint4 cs[2][HOT_WARPS * NPL * 32];
     uint4 sp[SCORE_CHUNK * 2];
     u32 m_s[SCORE_CHUNK];    // memory value of every pod of the chunk (ascending inside a run)
     u32 key_s[SCORE_CHUNK];  // run key: requirement group << 12 | class; a (group, class) run is contiguous in the sorted order
@@ -694,9 +700,12 @@ struct ScoreSmem {
     __align__(16) u32 cnt_s[DECIDE ? HOT_WARPS : 1][DECIDE ? SCORE_CHUNK : 4];   // DECIDE only: feasible nodes of the warp's slots
     __align__(16) u32 best_s[DECIDE ? HOT_WARPS : 1][DECIDE ? SCORE_CHUNK : 4];  // DECIDE only: lowest node index holding the warp's top score
     u32 mark_s[HOT_WARPS][SCORE_CHUNK / 32];           // bit i: the warp's entry for pod i is set (it holds until the next set bit)
+    u32 carry_s[HOT_WARPS][SCORE_CHUNK / 32];          // the warp's last marked pod before window k (window 0: pod 0, always marked)
 };
 
 // score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145).
+// The nodes' FreeMemory values and their contributions for the current run live in shared memory, so re-evaluating a
+// slot inside a run touches no global memory at all; only a run change fetches class-table entries (and clocks) from L2.
 // A warp does not walk the pods one by one.  After it has evaluated its nodes for pod i, everything it knows
 // stays valid up to the first later pod that either starts another (group, class) run or asks for more memory than
 // the smallest validity bound among its nodes -- and because the memory values ascend inside a run, that pod is
@@ -707,7 +716,7 @@ struct ScoreSmem {
 // lowest-index node holding the top score, packed as (score << 32 | ~index) so that one 64-bit
 // atomicMax across the node tiles yields the choice -- no output pass is needed at all.
 template <int NPL, bool DECIDE>
-__device__ __forceinline__ void score_body(ScoreSmem<DECIDE> &sm, int bar_id, u32 tid, u32 tile, u32 chunk, const DevSnap &s,
+__device__ __forceinline__ void score_body(ScoreSmem<NPL, DECIDE> &sm, int bar_id, u32 tid, u32 tile, u32 chunk, const DevSnap &s,
                                            const PodS *__restrict__ pods, u32 p_begin, u32 p_end, const u32 *__restrict__ tables,
                                            u64 *hilo, u64 *count, u64 *dkey, u32 chunk_pods) {
     const u32 lane = tid & 31, warp = tid >> 5;
@@ -722,7 +731,7 @@ __device__ __forceinline__ void score_body(ScoreSmem<DECIDE> &sm, int bar_id, u3
     if (tid < HOT_WARPS * (SCORE_CHUNK / 32)) (&sm.mark_s[0][0])[tid] = 0u;
     const u32 base = (tile * HOT_WARPS + warp) * (NPL * 32);
     u32 node[NPL], cardnum[NPL], stat[NPL];
-    bool ok[NPL];
+    bool ok[NPL], clkok[NPL];
 #pragma unroll
     for (int j = 0; j < NPL; ++j) {
         const u32 n = base + j * 32 + lane;
@@ -731,6 +740,11 @@ __device__ __forceinline__ void score_body(ScoreSmem<DECIDE> &sm, int bar_id, u3
         cardnum[j] = s.cardnum32[node[j]];
         stat[j] = in ? s.stat32[node[j]] : 0u;
         ok[j] = in && meta_table_node(s.meta[node[j]]);
+        clkok[j] = true;
+        const uint4 *src = reinterpret_cast<const uint4 *>(s.n32[F_FREE] + (size_t)node[j] * G);
+        const u32 slot = (warp * NPL + j) * 32 + lane;  // only this lane ever touches the slot: no barrier needed for it
+        sm.fr[0][slot] = src[0];
+        sm.fr[1][slot] = src[1];
     }
     half_sync(bar_id);
     u32 cur_key = 0xFFFFFFFFu;
@@ -744,11 +758,38 @@ __device__ __forceinline__ void score_body(ScoreSmem<DECIDE> &sm, int bar_id, u3
         cur_key = key;
 #pragma unroll
         for (int j = 0; j < NPL; ++j) {
+            const u32 slot = (warp * NPL + j) * 32 + lane;
+            if (!same) {  // a new run: this slot's contributions from the class table, the group's clock tests folded in
+                u32 cs[G];
+                load8(tables + ((size_t)pod.cls * s.cap + node[j]) * G, cs);
+                clkok[j] = true;
+                if (pod.has_clock) {  // warp-uniform
+                    u32 ck[G];
+                    load8(s.n32[F_CLOCK] + (size_t)node[j] * G, ck);
+                    u32 cnt = 0;
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        cnt += (ck[g] == pod.c) ? (cs[g] >> CS_HEALTH_SHIFT) : 0u;  // filter.go:56-58
+                        if (ck[g] < pod.c) cs[g] &= ~CS_SCORE_MASK;                  // collection.go:46 / algorithm.go:48
+                    }
+                    clkok[j] = cnt >= pod.reqC;
+                }
+                sm.cs[0][slot] = make_uint4(cs[0], cs[1], cs[2], cs[3]);
+                sm.cs[1][slot] = make_uint4(cs[4], cs[5], cs[6], cs[7]);
+            }
             if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
-                bool fit;
-                u32 b;
-                const u32 raw = hot_eval_mem(s, tables, node[j], pod.cls, pod.m, pod.num, pod.reqM, pod.has_clock, pod.c, pod.reqC, ok[j],
-                                             cardnum[j], stat[j], fit, b);
+                const uint4 f0 = sm.fr[0][slot], f1 = sm.fr[1][slot], c0 = sm.cs[0][slot], c1 = sm.cs[1][slot];
+                const u32 fr[G] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
+                const u32 cs[G] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+                u32 acc = 0, b = 0xFFFFFFFFu;
+#pragma unroll
+                for (int g = 0; g < G; ++g) {
+                    const bool q = fr[g] >= pod.m;  // filter.go:53 / collection.go:46 / algorithm.go:48
+                    b = q ? min(b, fr[g]) : b;
+                    acc += q ? cs[g] : 0u;
+                }
+                const bool fit = ok[j] && clkok[j] && (pod.num <= cardnum[j]) && ((acc >> CS_HEALTH_SHIFT) >= pod.reqM);
+                const u32 raw = stat[j] + (fit ? (acc & CS_SCORE_MASK) : 0u);
                 bound[j] = fit ? b : 0xFFFFFFFFu;  // a node that stopped fitting never fits again inside the run
                 hi_l[j] = fit ? raw : 0u;
                 lo_l[j] = fit ? raw : 0xFFFFFFFFu;
@@ -794,14 +835,20 @@ __device__ __forceinline__ void score_body(ScoreSmem<DECIDE> &sm, int bar_id, u3
         i = k;
     }
     half_sync(bar_id);
+    if (tid < HOT_WARPS * (SCORE_CHUNK / 32)) {  // per (warp, window): where the warp's last mark before the window sits
+        const u32 w = tid / (SCORE_CHUNK / 32), k0 = tid % (SCORE_CHUNK / 32);
+        u32 k = k0, m = 0;
+        while (!m && k) m = sm.mark_s[w][--k];
+        sm.carry_s[w][k0] = (k << 5) + (31 - __clz(m | 1u));
+    }
+    half_sync(bar_id);
     for (u32 i = tid; i < cn; i += HOT_THREADS) {
         u32 hi = 0, lo = 0xFFFFFFFFu, q[HOT_WARPS];
 #pragma unroll
         for (int w = 0; w < HOT_WARPS; ++w) {
             // the warp's entry for pod i sits at the last marked pod at or before i (pod 0 of a chunk is always marked)
-            u32 k = i >> 5, m = sm.mark_s[w][k] & (0xFFFFFFFFu >> (31 - (i & 31)));
-            while (!m && k) m = sm.mark_s[w][--k];
-            q[w] = (k << 5) + (31 - __clz(m | 1u));
+            const u32 k = i >> 5, m = sm.mark_s[w][k] & (0xFFFFFFFFu >> (31 - (i & 31)));
+            q[w] = m ? (k << 5) + (31 - __clz(m)) : sm.carry_s[w][k];
             hi = max(hi, sm.hi_s[w][q[w]]);
             lo = min(lo, sm.lo_s[w][q[w]]);
         }
@@ -986,14 +1033,15 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
 }
 
 #ifndef SCORE_MINB
-#define SCORE_MINB 4  // resident CTAs per SM the score pass is compiled for
+#define SCORE_MINB 4  // resident CTAs per SM the score pass is compiled for (its ~52 KB of shared memory allow four)
 #endif
 template <int NPL, bool DECIDE>
 __global__ void __launch_bounds__(HOT_THREADS, SCORE_MINB) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
                                                             const u32 *__restrict__ tables, u64 *hilo, u64 *count, u64 *dkey,
                                                             u32 chunk_pods,  // pods per CTA: a multiple of SCORE_BLK, <= SCORE_CHUNK
                                                             const u32 *gate) {  // non-null: run only while *gate == 0 (see gate_closed)
-    __shared__ ScoreSmem<DECIDE> sm;
+    extern __shared__ __align__(16) unsigned char score_smem_raw[];  // > 48 KB: dynamic (cudaFuncSetAttribute in yoda_create)
+    ScoreSmem<NPL, DECIDE> &sm = *reinterpret_cast<ScoreSmem<NPL, DECIDE> *>(score_smem_raw);
     if (gate_closed(gate, gate ? GATE_IF_ZERO : GATE_NONE)) return;
     score_body<NPL, DECIDE>(sm, 1, threadIdx.x, blockIdx.x, blockIdx.y, s, pods, p_begin, p_end, tables, hilo, count, dkey, chunk_pods);
 }

@@ -252,7 +252,11 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
     if (cudaDeviceGetAttribute(&c->n_sms, cudaDevAttrMultiProcessorCount, cfg->device) != cudaSuccess || c->n_sms <= 0) c->n_sms = 148;
     {
         int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fast_score<SCORE_NPL, false>, HOT_THREADS, 0) != cudaSuccess || per_sm <= 0) per_sm = 2;
+        // the score pass keeps its nodes in shared memory: more than the 48 KB a kernel gets without asking
+        if (cudaFuncSetAttribute(k_fast_score<SCORE_NPL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem<SCORE_NPL, false>)) != cudaSuccess ||
+            cudaFuncSetAttribute(k_fast_score<SCORE_NPL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem<SCORE_NPL, true>)) != cudaSuccess)
+            return bail(fail(YODA_E_CUDA, "cudaFuncSetAttribute(shared memory of the score pass) failed: %s", cudaGetErrorString(cudaGetLastError())));
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fast_score<SCORE_NPL, false>, HOT_THREADS, sizeof(ScoreSmem<SCORE_NPL, false>)) != cudaSuccess || per_sm <= 0) per_sm = 2;
         c->score_slots = (u32)per_sm * (u32)c->n_sms;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fast_out<4, true, false>, HOT_THREADS, 0) != cudaSuccess || per_sm <= 0) per_sm = 2;
         c->out_slots = (u32)per_sm * (u32)c->n_sms;
@@ -816,10 +820,10 @@ static int fast_score_launch(yoda_ctx *c, u32 p_begin, u32 p_end) {
     const dim3 grid(tiles, (p_end - p_begin + chunk - 1) / chunk);
     const u32 *gate = c->fw_gated ? &c->fw_ctl->err : nullptr;
     if (c->fw_decide_merged)
-        k_fast_score<SCORE_NPL, true><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
+        k_fast_score<SCORE_NPL, true><<<grid, HOT_THREADS, sizeof(ScoreSmem<SCORE_NPL, true>), c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
                                                                            c->d_count, c->d_ckey, chunk, gate);
     else
-        k_fast_score<SCORE_NPL, false><<<grid, HOT_THREADS, 0, c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
+        k_fast_score<SCORE_NPL, false><<<grid, HOT_THREADS, sizeof(ScoreSmem<SCORE_NPL, false>), c->stream>>>(c->snap, c->fw_pods, p_begin, p_end, c->fw_tables, c->d_hilo,
                                                                             c->d_count, c->d_ckey, chunk, gate);
     LAUNCHED(c);
     return YODA_OK;
