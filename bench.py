@@ -444,16 +444,20 @@ def main():
         step_e2e()
     barrier()
     w0 = time.perf_counter()
+    e2e_parts = [0.0, 0.0, 0.0]   # device-side H2D, kernels (first to last), D2H of each e2e step (CUDA events of the library)
     for _ in range(args.steps):
         step_e2e()
+        t = ctx.timing()
+        e2e_parts[0] += t.h2d_ms; e2e_parts[1] += t.total_ms; e2e_parts[2] += t.d2h_ms
     torch.cuda.synchronize()
     e2e_ms = (time.perf_counter() - w0) * 1e3 / max(args.steps, 1)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
+    e2e_parts = [v / max(args.steps, 1) for v in e2e_parts]
     if world > 1:
-        tt = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
+        tt = torch.tensor([ms, e2e_ms] + e2e_parts, device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms, e2e_ms = tt.tolist()
+        ms, e2e_ms, *e2e_parts = tt.tolist()
     total_nodes = n_nodes if pod_sharded else n_nodes * world
     total_pods = n_pods * world if pod_sharded else n_pods
     evals = float(total_pods) * total_nodes
@@ -481,7 +485,9 @@ def main():
                                    + (", Score matrix as uint32 (W = 5.125 B per evaluation)" if flags & api.EVAL_RAW32 else ""),
                        "l2": "every step writes the result matrices (>> 126 MB L2), which sweeps L2 between iterations; the snapshot is L2-resident by design",
                        "path": "narrow-fast" if t_last.path == 1 else "direct-u64", "classes": t_last.n_classes, "groups": t_last.n_groups},
-            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(reqs_np.nbytes), "d2h_bytes_per_step": int(n_pods * api.POD_RES.itemsize)},
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(reqs_np.nbytes), "d2h_bytes_per_step": int(n_pods * api.POD_RES.itemsize),
+                    "breakdown_ms": {"h2d": e2e_parts[0], "kernels": e2e_parts[1], "d2h": e2e_parts[2],
+                                     "note": "CUDA events of the library inside the e2e steps, max over ranks; the rest of ms_per_step is host time (launches, read-backs, waiting for the slowest rank)"}},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "output pass (write_ms)", "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
