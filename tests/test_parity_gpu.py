@@ -658,3 +658,36 @@ def test_mostly_wide_snapshot_goes_direct():
     res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_FULL)
     assert t.path == 0
     assert_matches_oracle(snap, labels, res, mats)
+
+
+def test_counts_left_on_the_device_and_their_redo():
+    """From its second batch on a context sizes nothing from read-backs: group and class counts stay on the device and a
+    batch that does not fit what earlier batches sized (more classes than the table buffer holds, more classes than any
+    buffer may hold, more groups than the limit) is flagged there and redone with the counts read back.  Every batch of
+    the sequence against the oracle, on one long-lived context."""
+    n_nodes = 700
+    nodes = []
+    for i in range(n_nodes):
+        cards = [{"health": "Healthy", "free": 8 * i + g + 1, "total": 1_000_000 - (8 * i + g), "clock": 1000, "core": 10, "bandwidth": 10, "power": 10}
+                 for g in range(8)]
+        nodes.append({"name": f"n{i}", "has_scv": True, "card_number": 8 + 40 * i, "cards": cards, "free_sum": sum(c["free"] for c in cards),
+                      "total_sum": sum(c["total"] for c in cards), "pods": []})
+    snap = Snapshot.from_nodes(nodes)
+    many_classes = [{"scv/memory": str(m)} for m in range(1, 5201)]      # MaxTotalMemory differs for every pod
+    many_groups = [{"scv/number": str(i)} for i in range(6000)]          # one requirement group per pod
+    plan = [("few classes", many_classes[:30], 1), ("more classes than the buffer", many_classes[:500], 1), ("again, now it fits", many_classes[100:600], 1),
+            ("more classes than any buffer", many_classes, 0), ("back to few", many_classes[:40], 1), ("too many groups", many_groups, 0),
+            ("and a normal batch", many_classes[:300], 1)]
+    with api.Context(n_nodes) as ctx:
+        ctx.load_snapshot(snap)
+        for what, labels, path in plan:
+            for flags in (api.EVAL_FULL, api.EVAL_DECIDE):
+                res = ctx.eval(pods_to_requests(labels), flags)
+                assert ctx.timing().path == path, what
+                mats = ctx.fetch_all(min(len(labels), 60)) if flags & api.EVAL_FULL else None
+                o = ora.OracleCluster.from_snapshot(snap).eval(labels, threads=8)
+                if mats is not None:
+                    o_small = {k: (v[:60] if k in ("feasible", "raw", "norm") else v) for k, v in o.items()}
+                    assert_matches_oracle(snap, labels, res, mats, o=o_small, what=what)
+                else:
+                    assert_matches_oracle(snap, labels, res, None, o=o, what=what)

@@ -419,7 +419,7 @@ __global__ void k_class_assign(PodS *pods, u32 P, const u64 *__restrict__ max6, 
     }
     if (!same) atomicOr(&ctl->err, FAST_ERR_HASH);
     if (!narrow) atomicOr(&ctl->err, FAST_ERR_WIDE_CLASS);
-    pods[i].cls = cid;
+    pods[i].cls = cid < ccap ? cid : 0u;  // (a batch over the capacity is flagged and redone; until then no table index may leave the buffer)
     if (cid >= ccap) {
         atomicOr(&ctl->err, FAST_ERR_CAP);
     } else if (orig == r) {
@@ -427,6 +427,10 @@ __global__ void k_class_assign(PodS *pods, u32 P, const u64 *__restrict__ max6, 
         for (int f = 0; f < 6; ++f) cls_max[(size_t)cid * 6 + f] = (u32)max6[(size_t)r * 6 + f];
     }
 }
+
+// Node-sharded batches that ran with the counts on the device: 1 if this shard hit a capacity limit (the batch has to
+// be redone the careful way); all-reduced with MAX so that every shard takes the same decision.
+__global__ void k_cap_flag(const FastCtl *__restrict__ ctl, u64 *flag) { *flag = (ctl->err & FAST_ERR_CAP) ? 1ull : 0ull; }
 
 // Per class, per card: CalculateCardScore (algorithm.go:57-68) packed with the card's health bit.
 // A card whose fields exceed the class maxima can never be scored by a pod of that class (it would
@@ -463,9 +467,12 @@ struct ClassConsts {
     u32 plain;    // some maximum is 1
 };
 
+// count_on_device: the class count is taken from ctl (the host sized the grid for the table capacity instead of
+// reading the count back); surplus blocks leave at once.
 __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__restrict__ cls_max, u32 n_classes, u32 *tables,
-                                                       FastCtl *ctl) {
+                                                       FastCtl *ctl, bool count_on_device) {
     __shared__ ClassConsts cc[CLS_PER];
+    if (count_on_device) n_classes = min(n_classes, ctl->n_classes);
     const u32 cid0 = blockIdx.y * CLS_PER;
     if (cid0 >= n_classes) return;
     const u32 ncls = min((u32)CLS_PER, n_classes - cid0);

@@ -174,6 +174,9 @@ struct yoda_ctx {
     bool fw_defer_groups = false;  // the group count stays on the device until the class count is read back
     bool fw_gate_ok = false;       // node-sharded FULL batch: fast/exact path selected on the device by FastCtl::err ...
     bool fw_gated = false;         // ... and this evaluation is running that way (both paths launched, see gate_closed)
+    bool fw_opt_ok = false;        // the class count may stay on the device too (tables sized by an earlier batch) ...
+    bool fw_optimistic = false;    // ... and this evaluation is running that way: no host round trip in the middle of a batch
+    bool fw_no_opt = false;        // set while a batch that hit a capacity limit is redone with the counts read back
     bool fw_decide_merged = false;
     bool fw_groups_pending = false;  // the group count (and its capacity check) has not been read back yet
     // sequential-commit scratch
@@ -873,7 +876,7 @@ static int fast_classes(yoda_ctx *c) {
             c->fw_tables_classes = want;
         }
         if (N) {
-            k_class_tables<<<dim3((N + CLST - 1) / CLST, (P + CLS_PER - 1) / CLS_PER), CLST, 0, st>>>(c->snap, c->fw_cls_max, P, c->fw_tables, c->fw_ctl);
+            k_class_tables<<<dim3((N + CLST - 1) / CLST, (P + CLS_PER - 1) / CLS_PER), CLST, 0, st>>>(c->snap, c->fw_cls_max, P, c->fw_tables, c->fw_ctl, false);
             LAUNCHED(c);
         }
         if (c->fw_allow_defer) {
@@ -894,6 +897,26 @@ static int fast_classes(yoda_ctx *c) {
     LAUNCHED(c);
     k_hash_compact<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_ckeys, c->fw_cids, c->fw_htab, &c->fw_ctl->n_classes);
     LAUNCHED(c);
+    // Steady state: the table buffer an earlier batch sized holds this batch's classes too.  Then nothing is read back
+    // here: the class count stays on the device (grid sized for the buffer, surplus blocks leave), a class beyond the
+    // buffer raises FAST_ERR_CAP, and the end of the evaluation (settle_locked) redoes such a batch with the counts read
+    // back.  No host round trip in the middle of a batch, hence no idle GPU and, node-sharded, no skew between the shards.
+    if (c->fw_opt_ok && c->fw_tables_classes > 0) {
+        const u32 cap_now = std::min(ccap, c->fw_tables_classes);
+        k_class_assign<<<pb, 256, 0, st>>>(c->fw_pods, P, c->d_max6, c->fw_crep, c->fw_cids, c->fw_slot, c->fw_cls_max, cap_now, c->fw_ctl);
+        LAUNCHED(c);
+        if (N) {
+            dim3 grid((N + CLST - 1) / CLST, (cap_now + CLS_PER - 1) / CLS_PER);
+            k_class_tables<<<grid, CLST, 0, st>>>(c->snap, c->fw_cls_max, cap_now, c->fw_tables, c->fw_ctl, true);
+            LAUNCHED(c);
+        }
+        c->fw_optimistic = true;
+        if (c->fw_allow_defer)
+            c->fw_deferred_err = true;
+        else
+            c->fw_gated = true;  // fw_opt_ok is only set with one of the two
+        return YODA_OK;
+    }
     k_class_assign<<<pb, 256, 0, st>>>(c->fw_pods, P, c->d_max6, c->fw_crep, c->fw_cids, c->fw_slot, c->fw_cls_max, ccap, c->fw_ctl);
     LAUNCHED(c);
     TRY(fast_read_ctl(c));
@@ -925,7 +948,7 @@ static int fast_classes(yoda_ctx *c) {
     }
     if (N) {
         dim3 grid((N + CLST - 1) / CLST, (c->fw_n_classes + CLS_PER - 1) / CLS_PER);
-        k_class_tables<<<grid, CLST, 0, st>>>(c->snap, c->fw_cls_max, c->fw_n_classes, c->fw_tables, c->fw_ctl);
+        k_class_tables<<<grid, CLST, 0, st>>>(c->snap, c->fw_cls_max, c->fw_n_classes, c->fw_tables, c->fw_ctl, false);
         LAUNCHED(c);
     }
     if (c->fw_allow_defer) {
@@ -1029,6 +1052,8 @@ static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
     c->fw_gated = false;
     c->fw_gate_ok = false;
     c->fw_defer_groups = false;
+    c->fw_opt_ok = false;
+    c->fw_optimistic = false;
     c->ph_done = -1;
     c->last_P = 0;
     c->last_full = false;
@@ -1080,6 +1105,8 @@ static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
     c->fw_allow_defer = (c->comm == nullptr);
     c->fw_defer_groups = true;
     c->fw_gate_ok = (c->comm != nullptr) && (c->ph_flags & YODA_EVAL_FULL);
+    c->fw_opt_ok = !c->fw_no_opt && (c->fw_allow_defer || c->fw_gate_ok);
+    c->fw_optimistic = false;
     c->fw_deferred_err = false;
     c->fw_decide_merged = (c->comm == nullptr) && !(c->ph_flags & YODA_EVAL_FULL) && c->ph_path == 1;
     c->fw_agree = (c->comm != nullptr) && !(c->ph_flags & YODA_EVAL_FULL);
@@ -1090,9 +1117,15 @@ static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
     TRY(phase2(c));
     TRY(exchange_locked(c, 2));
     TRY(phase3(c));
+    if (c->comm && c->fw_optimistic) {  // every shard must take the same "redo" decision (settle_locked)
+        k_cap_flag<<<1, 1, 0, c->stream>>>(c->fw_ctl, c->d_agree);
+        LAUNCHED(c);
+        NC(g_nccl.AllReduce(c->d_agree, c->d_agree, 1, ncclUint64, ncclMax, c->comm, c->stream));
+    }
     c->fw_allow_defer = false;
     c->fw_defer_groups = false;
     c->fw_gate_ok = false;
+    c->fw_opt_ok = false;
     c->fw_agree = false;
     c->ph_done = 3;
     c->last_P = c->ph_P;
@@ -1124,6 +1157,51 @@ static void gate_verdict(yoda_ctx *c) {
     }
 }
 
+// After run_all_locked: bring the verdicts that were left on the device to the host (one synchronisation) and do what
+// they ask for.  *redone = the evaluation was repeated (results must be fetched again).  Leaves the stream synchronised
+// whenever it had anything to settle.
+static int settle_locked(yoda_ctx *c, const yoda_pod_req *d_req, bool *redone) {
+    *redone = false;
+    for (int round = 0; round < 3; ++round) {
+        if (!(c->fw_deferred_err || c->fw_gated || c->fw_optimistic)) return YODA_OK;
+        cudaStream_t st = c->stream;
+        const bool collective = c->comm && c->fw_optimistic;
+        CU(cudaMemcpyAsync(c->fw_hctl, c->fw_ctl, sizeof(FastCtl), cudaMemcpyDeviceToHost, st));
+        if (collective) CU(cudaMemcpyAsync(c->h_agree, c->d_agree, sizeof(u64), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (c->fw_optimistic) {  // the counts this evaluation ran without
+            c->fw_n_classes = c->fw_hctl->n_classes;
+            c->fw_n_groups = c->fw_hctl->n_groups;
+            c->fw_groups_pending = false;
+        }
+        const bool over = c->fw_optimistic && ((c->fw_hctl->err & FAST_ERR_CAP) || (collective && *c->h_agree));
+        c->fw_optimistic = false;
+        if (over) {
+            // more classes than the table buffer holds, or more groups than the limit (on some shard): once more with the
+            // counts read back, which grows the buffer or hands the batch to the exact kernels
+            c->fw_no_opt = true;
+            c->ph_path = 1;
+            c->fw_gated = false;
+            c->fw_deferred_err = false;
+            const int rc = run_all_locked(c, d_req);
+            c->fw_no_opt = false;
+            TRY(rc);
+            *redone = true;
+            continue;
+        }
+        gate_verdict(c);
+        if (c->fw_deferred_err) {
+            c->fw_deferred_err = false;
+            if (c->fw_hctl->err) {
+                TRY(redo_direct_if_flagged(c, d_req, c->fw_hctl->err));
+                *redone = true;
+            }
+        }
+        return YODA_OK;
+    }
+    return fail(YODA_E_STATE, "evaluation did not settle");
+}
+
 #define STAGE_PODS 4096u  // batches up to this size go through the library's pinned staging buffers
 extern "C" int yoda_eval_batch(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32 flags, yoda_pod_result *out) {
     if (!c || (P && (!pods || !out))) return fail(YODA_E_ARG, "null argument");
@@ -1142,16 +1220,10 @@ extern "C" int yoda_eval_batch(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32
     CU(cudaEventRecord(c->ev[EV_D2H0], st));
     CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
     CU(cudaEventRecord(c->ev[EV_D2H1], st));
-    const bool deferred = c->fw_deferred_err;
-    if (deferred || c->fw_gated) CU(cudaMemcpyAsync(c->fw_hctl, c->fw_ctl, sizeof(FastCtl), cudaMemcpyDeviceToHost, st));
+    bool redone = false;
+    TRY(settle_locked(c, c->d_req, &redone));  // the read-back of the verdicts rides on the same synchronisation as the results
+    if (redone) CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
-    gate_verdict(c);
-    if (deferred && c->fw_hctl->err) {
-        TRY(redo_direct_if_flagged(c, c->d_req, c->fw_hctl->err));
-        CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
-    }
-    c->fw_deferred_err = false;
     if (staged) memcpy(out, c->h_res, (size_t)P * sizeof(yoda_pod_result));
     collect_timing(c, true);
     return YODA_OK;
@@ -1164,14 +1236,8 @@ extern "C" int yoda_eval_batch_device(yoda_ctx *c, const void *d_pods, u32 P, u3
     if (P == 0) return YODA_OK;
     TRY(begin_locked(c, P, flags));
     TRY(run_all_locked(c, (const yoda_pod_req *)d_pods));
-    if (c->fw_gated) {
-        TRY(fast_read_ctl(c));
-        gate_verdict(c);
-    }
-    if (c->fw_deferred_err) {
-        TRY(fast_read_ctl(c));
-        TRY(redo_direct_if_flagged(c, (const yoda_pod_req *)d_pods, c->fw_hctl->err));
-    }
+    bool redone = false;
+    TRY(settle_locked(c, (const yoda_pod_req *)d_pods, &redone));
     if (d_out)
         CU(cudaMemcpyAsync(d_out, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToDevice, c->stream));
     return YODA_OK;
