@@ -414,7 +414,8 @@ def main():
 
     def step_e2e():
         tick()
-        api.check(ctx.L.yoda_eval_batch(ctx.h, h_view.ctypes.data, n_pods, flags, h_out.data_ptr()))
+        # node-sharded: after the exchanges every shard holds the same per-pod results; rank 0 reads them, the others pass NULL
+        api.check(ctx.L.yoda_eval_batch(ctx.h, h_view.ctypes.data, n_pods, flags, h_out.data_ptr() if (rank == 0 or pod_sharded) else None))
 
     for _ in range(args.warmup):
         step_device()
@@ -486,6 +487,7 @@ def main():
                        "l2": "every step writes the result matrices (>> 126 MB L2), which sweeps L2 between iterations; the snapshot is L2-resident by design",
                        "path": "narrow-fast" if t_last.path == 1 else "direct-u64", "classes": t_last.n_classes, "groups": t_last.n_groups},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(reqs_np.nbytes), "d2h_bytes_per_step": int(n_pods * api.POD_RES.itemsize),
+                    "d2h_note": "per-pod results (72 B per pod) read by rank 0; node shards hold identical copies and do not read theirs back",
                     "breakdown_ms": {"h2d": e2e_parts[0], "kernels": e2e_parts[1], "d2h": e2e_parts[2],
                                      "note": "CUDA events of the library inside the e2e steps, max over ranks; the rest of ms_per_step is host time (launches, read-backs, waiting for the slowest rank)"}},
             "gpu_launches": int(launches),

@@ -140,6 +140,8 @@ int yoda_node_count(yoda_ctx *ctx, uint32_t *n_nodes); /* highest committed inde
  *      Yoda.Filter (scheduler.go:76-93) for every node, Yoda.PostFilter/CollectMaxValues
  *      (scheduler.go:95-103, collection.go:30-57), Yoda.Score (scheduler.go:109-130) and
  *      Yoda.NormalizeScore (scheduler.go:132-157), plus the lowest-index argmax. ---- */
+/* out may be NULL: the batch is evaluated and its matrices kept, but no per-pod results are copied back.  For node shards
+ * whose host does not consume them -- after the exchanges every shard holds the same per-pod results, one copy is enough. */
 int yoda_eval_batch(yoda_ctx *ctx, const yoda_pod_req *pods, uint32_t n_pods, uint32_t flags, yoda_pod_result *out);
 /* same, with `d_pods` (n_pods * sizeof(yoda_pod_req)) and `d_out` (n_pods * sizeof(yoda_pod_result),
  * may be NULL) already in device memory; asynchronous on the context's stream */

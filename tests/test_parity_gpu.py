@@ -691,3 +691,20 @@ def test_counts_left_on_the_device_and_their_redo():
                     assert_matches_oracle(snap, labels, res, mats, o=o_small, what=what)
                 else:
                     assert_matches_oracle(snap, labels, res, None, o=o, what=what)
+
+
+def test_eval_without_reading_results_back():
+    """yoda_eval_batch(out = NULL): the batch is evaluated and its matrices kept; nothing is copied to the host.  What a node
+    shard does when another shard's host consumes the (identical) per-pod results."""
+    snap = synth.make_snapshot(900)
+    reqs = synth.make_requests(70, 13)
+    with api.Context(900) as ctx:
+        ctx.load_snapshot(snap)
+        want = ctx.eval(reqs, api.EVAL_FULL)
+        want_rows = ctx.fetch_all(5)
+        for n in (70, 3):
+            api.check(ctx.L.yoda_eval_batch(ctx.h, reqs.ctypes.data, n, api.EVAL_FULL, None))
+            rows = ctx.fetch_all(min(n, 5))
+            for k in rows:
+                assert np.array_equal(rows[k], want_rows[k][:min(n, 5)]), k
+        assert np.array_equal(ctx.eval(reqs, api.EVAL_FULL), want)

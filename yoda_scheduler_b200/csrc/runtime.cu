@@ -1204,7 +1204,7 @@ static int settle_locked(yoda_ctx *c, const yoda_pod_req *d_req, bool *redone) {
 
 #define STAGE_PODS 4096u  // batches up to this size go through the library's pinned staging buffers
 extern "C" int yoda_eval_batch(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32 flags, yoda_pod_result *out) {
-    if (!c || (P && (!pods || !out))) return fail(YODA_E_ARG, "null argument");
+    if (!c || (P && !pods)) return fail(YODA_E_ARG, "null argument");
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard dg(c->cfg.device);
     if (P == 0) return YODA_OK;
@@ -1218,13 +1218,13 @@ extern "C" int yoda_eval_batch(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32
     TRY(run_all_locked(c, c->d_req));
     yoda_pod_result *dst = staged ? c->h_res : out;
     CU(cudaEventRecord(c->ev[EV_D2H0], st));
-    CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
+    if (out) CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
     CU(cudaEventRecord(c->ev[EV_D2H1], st));
     bool redone = false;
     TRY(settle_locked(c, c->d_req, &redone));  // the read-back of the verdicts rides on the same synchronisation as the results
-    if (redone) CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
+    if (redone && out) CU(cudaMemcpyAsync(dst, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
-    if (staged) memcpy(out, c->h_res, (size_t)P * sizeof(yoda_pod_result));
+    if (staged && out) memcpy(out, c->h_res, (size_t)P * sizeof(yoda_pod_result));
     collect_timing(c, true);
     return YODA_OK;
 }
