@@ -141,13 +141,17 @@ def _nccl_worker_body(rank, world, port, N, P, out_dir):
     dist.destroy_process_group()
 
 
-def test_two_gpus_nccl(tmp_path):
+@pytest.mark.parametrize("xchg", ["nccl", "peer"])
+def test_two_gpus_nccl(tmp_path, xchg, monkeypatch):
+    """Two processes, two GPUs, the exchanges inside the library: over NCCL (default) and over peer memory
+    (YODA_B200_XCHG=peer: CUDA-IPC mapped arenas, publish / reduce kernels of csrc/xchg_kernels.cuh)."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
     import torch.multiprocessing as mp
     N, P, world = 4000, 600, 2
-    port = 29500 + os.getpid() % 2000
+    port = 29500 + (os.getpid() + (7 if xchg == "peer" else 0)) % 2000
+    monkeypatch.setenv("YODA_B200_XCHG", xchg)     # the spawned shards inherit it
     mp.spawn(_nccl_worker, args=(world, port, N, P, str(tmp_path)), nprocs=world, join=True)
     reqs = synth.make_requests(P, 31)
     snap = synth.make_snapshot(N)

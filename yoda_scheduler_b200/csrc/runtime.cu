@@ -19,6 +19,7 @@
 #include "fast_kernels.cuh"
 #include "seq_kernels.cuh"
 #include "tail_kernels.cuh"
+#include "xchg_kernels.cuh"
 
 // ------------------------------------------------------------------------------------------
 // errors
@@ -52,6 +53,7 @@ struct NcclApi {
     ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
@@ -71,6 +73,7 @@ static int nccl_load() {
     SYM(GetUniqueId);
     SYM(CommInitRank);
     SYM(AllReduce);
+    SYM(AllGather);
     SYM(GroupStart);
     SYM(GroupEnd);
     SYM(CommDestroy);
@@ -152,6 +155,16 @@ struct yoda_ctx {
     size_t h_rows_cap = 0;
     // NCCL
     ncclComm_t comm = nullptr;
+    // exchanges over peer memory (xchg_kernels.cuh): this shard's arena, the other shards' arenas mapped through CUDA IPC
+    bool x_ok = false;             // the peer path is set up on EVERY shard (agreed collectively); otherwise NCCL does the exchanges
+    u64 *x_arena = nullptr;
+    u32 x_cap = 0;                 // pods per parity the arenas hold
+    XPeers x_peers{};
+    void *x_opened[X_MAX_RANKS]{};  // IPC mappings to close
+    u8 *x_handles = nullptr;       // device scratch of the handle all-gather
+    u32 *x_done = nullptr, *x_err = nullptr;
+    u64 x_seq = 0;                 // sharded batches so far: the same on every shard
+    u32 x_gen[X_PHASES]{};         // exchanges of each phase inside the current batch (a redo repeats phase 0)
     u64 *d_agree = nullptr, *h_agree = nullptr;  // one word all-reduced before a sharded DECIDE score pass (see phase1)
     bool fw_agree = false;                       // this evaluation may ask the other shards which kernels they run
     // fast (narrow) path workspace
@@ -322,10 +335,20 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
     return YODA_OK;
 }
 
+static int nccl_host_barrier(yoda_ctx *c, u64 mine, int op_min, u64 *result);
+static void xchg_release(yoda_ctx *c);
+
 extern "C" void yoda_destroy(yoda_ctx *c) {
     if (!c) return;
     DeviceGuard dg(c->cfg.device);
     cudaDeviceSynchronize();
+    if (c->comm && c->x_ok) {
+        // a peer may still be reading this shard's arena: leave together (yoda_destroy of a sharded context is collective)
+        u64 dummy;
+        nccl_host_barrier(c, 0, 0, &dummy);
+    }
+    xchg_release(c);
+    dev_free(c->x_handles); dev_free(c->x_done); dev_free(c->x_err);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     dev_free(c->d_agree);
     if (c->h_agree) cudaFreeHost(c->h_agree);
@@ -1060,9 +1083,138 @@ static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
     return YODA_OK;
 }
 
+// ---- exchanges over peer memory ---------------------------------------------------------------
+// An all-reduce of one word over NCCL followed by a host wait: the barrier of the (rare) collective set-up steps.
+static int nccl_host_barrier(yoda_ctx *c, u64 mine, int op_min, u64 *result) {
+    CU(cudaMemcpyAsync(c->d_agree, &mine, sizeof(u64), cudaMemcpyHostToDevice, c->stream));
+    NC(g_nccl.AllReduce(c->d_agree, c->d_agree, 1, ncclUint64, op_min ? ncclMin : ncclMax, c->comm, c->stream));
+    CU(cudaMemcpyAsync(c->h_agree, c->d_agree, sizeof(u64), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (result) *result = *c->h_agree;
+    return YODA_OK;
+}
+
+static void xchg_release(yoda_ctx *c) {
+    for (u32 r = 0; r < X_MAX_RANKS; ++r) {
+        if (c->x_opened[r]) cudaIpcCloseMemHandle(c->x_opened[r]);
+        c->x_opened[r] = nullptr;
+        c->x_peers.arena[r] = nullptr;
+    }
+    dev_free(c->x_arena);
+    c->x_cap = 0;
+    c->x_ok = false;
+    cudaGetLastError();
+}
+
+// (Re)build the arenas for `cap` pods.  Collective: every shard calls it for the same batch.  Any failure on any shard
+// (no IPC between these processes, no peer access, more than 8 shards), or YODA_B200_XCHG != peer, leaves ALL shards on NCCL.
+static int xchg_setup(yoda_ctx *c, u32 cap) {
+    const u32 R = c->cfg.shard_count, me = c->cfg.shard_rank;
+    cudaStream_t st = c->stream;
+    // nobody may still be reading an arena that is about to go away
+    TRY(nccl_host_barrier(c, 0, 0, nullptr));
+    xchg_release(c);
+    // Opt-in (YODA_B200_XCHG=peer): measured on 8 B200s the one-shot exchange does not beat NCCL's all-reduce (config 3:
+    // 8.38 vs 8.32 ms per step, config 4: 3.32 vs 3.31 ms) -- every shard pulls 7x the payload over NVLink where NCCL
+    // reduces in two steps (and in the switch); it stays as the path without NCCL launches on the stream.
+    const char *mode = getenv("YODA_B200_XCHG");
+    u64 ok = (R <= X_MAX_RANKS && g_nccl.AllGather && mode && !strcmp(mode, "peer")) ? 1 : 0;
+    cudaIpcMemHandle_t mine{}, all[X_MAX_RANKS]{};
+    if (ok) {
+        if (!c->x_handles && dev_alloc(&c->x_handles, (size_t)X_MAX_RANKS * sizeof(cudaIpcMemHandle_t))) ok = 0;
+        if (ok && !c->x_done && (dev_alloc(&c->x_done, 1) || dev_alloc(&c->x_err, 1))) ok = 0;
+        if (ok && dev_alloc(&c->x_arena, x_arena_words(cap))) ok = 0;
+        if (ok && (cudaMemsetAsync(c->x_arena, 0, x_arena_words(cap) * sizeof(u64), st) != cudaSuccess ||
+                   cudaMemsetAsync(c->x_done, 0, sizeof(u32), st) != cudaSuccess || cudaMemsetAsync(c->x_err, 0, sizeof(u32), st) != cudaSuccess ||
+                   cudaIpcGetMemHandle(&mine, c->x_arena) != cudaSuccess))
+            ok = 0;
+        cudaGetLastError();
+    }
+    // every shard takes part in the gather whatever its own state (the collectives must match)
+    if (g_nccl.AllGather && c->x_handles) {
+        CU(cudaMemcpyAsync(c->x_handles + (size_t)me * sizeof mine, &mine, sizeof mine, cudaMemcpyHostToDevice, st));
+        NC(g_nccl.AllGather(c->x_handles + (size_t)me * sizeof mine, c->x_handles, sizeof mine, ncclChar, c->comm, st));
+        CU(cudaMemcpyAsync(all, c->x_handles, (size_t)R * sizeof mine, cudaMemcpyDeviceToHost, st));
+    }
+    u64 all_ok = 0;
+    TRY(nccl_host_barrier(c, ok, 1, &all_ok));  // also: every arena is cleared before any peer raises a flag in it
+    if (all_ok) {
+        for (u32 r = 0; r < R && ok; ++r) {
+            if (r == me) {
+                c->x_peers.arena[r] = c->x_arena;
+                continue;
+            }
+            void *p = nullptr;
+            if (cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cudaGetLastError();
+                ok = 0;
+                break;
+            }
+            c->x_opened[r] = p;
+            c->x_peers.arena[r] = (u64 *)p;
+        }
+        TRY(nccl_host_barrier(c, ok, 1, &all_ok));
+    }
+    if (!all_ok) {
+        xchg_release(c);
+        return YODA_OK;  // NCCL carries the exchanges
+    }
+    c->x_cap = cap;
+    c->x_ok = true;
+    return YODA_OK;
+}
+
+// one partial buffer through the arenas: publish (the last buffer of the exchange raises the flags), then reduce
+static int xchg_one(yoda_ctx *c, int phase, u64 *buf, size_t slot_off, size_t n, int op, bool last, bool reduce_now) {
+    const u32 R = c->cfg.shard_count, me = c->cfg.shard_rank, par = (u32)(c->x_seq & 1u);
+    const u64 tag = c->x_seq * 8 + c->x_gen[phase];
+    const size_t voff = x_values_off(c->x_cap, par) + slot_off, foff = x_flags_off(c->x_cap, par, (u32)phase);
+    const u32 blocks = (u32)std::min<size_t>((n + 255) / 256, 592);
+    if (!reduce_now) {
+        k_x_publish<<<blocks, 256, 0, c->stream>>>(buf, c->x_arena + voff, n, c->x_done, c->x_peers, foff, me, R, tag, last ? 1 : 0);
+    } else {
+        k_x_reduce<<<blocks, 256, 0, c->stream>>>(c->x_peers, voff, buf, n, op, c->x_arena + foff, R, tag, c->x_err);
+    }
+    LAUNCHED(c);
+    return YODA_OK;
+}
+
+struct XBuf {
+    u64 *buf;
+    size_t off, n;
+    int op;
+};
+static int xchg_phase(yoda_ctx *c, int phase, const XBuf *b, int nb) {
+    for (int i = 0; i < nb; ++i) TRY(xchg_one(c, phase, b[i].buf, b[i].off, b[i].n, b[i].op, i == nb - 1, false));
+    for (int i = 0; i < nb; ++i) TRY(xchg_one(c, phase, b[i].buf, b[i].off, b[i].n, b[i].op, false, true));
+    c->x_gen[phase]++;
+    return YODA_OK;
+}
+
 static int exchange_locked(yoda_ctx *c, int phase) {
     if (!c->comm) return YODA_OK;
     const u32 P = c->ph_P;
+    if (c->x_ok) {
+        // arena slots per parity, in pods: max6 [0, 6 cap), hilo [6 cap, 8 cap), ckey [8 cap, 9 cap), count [9 cap, 10 cap)
+        const size_t cap = c->x_cap;
+        const XBuf max6{c->d_max6, 0, (size_t)P * 6, 0}, hilo{c->d_hilo, cap * 6, (size_t)P * 2, 0}, ckey{c->d_ckey, cap * 8, P, 0},
+            count{c->d_count, cap * 9, P, 1};
+        if (phase == 0) {
+            TRY(xchg_phase(c, 0, &max6, 1));
+        } else if (phase == 1) {
+            const XBuf all[3] = {hilo, ckey, count};
+            TRY(xchg_phase(c, 1, all, c->fw_decide_merged ? 3 : 1));
+        } else if (phase == 2 && !c->fw_decide_merged) {
+            // with the counts left on the device, "a shard hit a capacity limit" rides along (settle_locked reads it)
+            if (c->fw_optimistic) {
+                k_cap_flag<<<1, 1, 0, c->stream>>>(c->fw_ctl, c->d_agree);
+                LAUNCHED(c);
+            }
+            const XBuf all[3] = {ckey, count, XBuf{c->d_agree, cap * X_WORDS_PER_POD, 1, 0}};
+            TRY(xchg_phase(c, 2, all, c->fw_optimistic ? 3 : 2));
+        }
+        return YODA_OK;
+    }
     if (phase == 0) {
         NC(g_nccl.AllReduce(c->d_max6, c->d_max6, (size_t)P * 6, ncclUint64, ncclMax, c->comm, c->stream));
     } else if (phase == 1) {
@@ -1102,6 +1254,18 @@ static void collect_timing(yoda_ctx *c, bool copies) {
 }
 
 static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
+    if (c->comm) {
+        // exchanges over peer memory: arenas sized like the pod buffers (every shard sees the same batches, so they all
+        // grow at the same batch); a new batch flips the parity of the arena halves
+        const char *xmode = getenv("YODA_B200_XCHG");
+        if (!(xmode && !strcmp(xmode, "peer")) && c->x_cap == 0) c->x_cap = 0xFFFFFFFFu;  // NCCL (default): no set-up collectives at all
+        if (c->ph_P > c->x_cap && (c->x_ok || c->x_cap == 0)) {
+            TRY(xchg_setup(c, c->pods_cap));
+            if (!c->x_ok) c->x_cap = 0xFFFFFFFFu;  // decided: NCCL; do not try again for every batch
+        }
+        c->x_seq++;
+        c->x_gen[0] = c->x_gen[1] = c->x_gen[2] = 0;
+    }
     c->fw_allow_defer = (c->comm == nullptr);
     c->fw_defer_groups = true;
     c->fw_gate_ok = (c->comm != nullptr) && (c->ph_flags & YODA_EVAL_FULL);
@@ -1117,7 +1281,7 @@ static int run_all_locked(yoda_ctx *c, const yoda_pod_req *d_req) {
     TRY(phase2(c));
     TRY(exchange_locked(c, 2));
     TRY(phase3(c));
-    if (c->comm && c->fw_optimistic) {  // every shard must take the same "redo" decision (settle_locked)
+    if (c->comm && c->fw_optimistic && !c->x_ok) {  // every shard must take the same "redo" decision (settle_locked)
         k_cap_flag<<<1, 1, 0, c->stream>>>(c->fw_ctl, c->d_agree);
         LAUNCHED(c);
         NC(g_nccl.AllReduce(c->d_agree, c->d_agree, 1, ncclUint64, ncclMax, c->comm, c->stream));
@@ -1163,12 +1327,21 @@ static void gate_verdict(yoda_ctx *c) {
 static int settle_locked(yoda_ctx *c, const yoda_pod_req *d_req, bool *redone) {
     *redone = false;
     for (int round = 0; round < 3; ++round) {
-        if (!(c->fw_deferred_err || c->fw_gated || c->fw_optimistic)) return YODA_OK;
+        if (!(c->fw_deferred_err || c->fw_gated || c->fw_optimistic)) {
+            if (c->x_ok) {  // a shard that waited in vain for a peer must not hand out what it computed
+                CU(cudaMemcpyAsync(&c->h_agree[1], c->x_err, sizeof(u32), cudaMemcpyDeviceToHost, c->stream));
+                CU(cudaStreamSynchronize(c->stream));
+                if ((u32)c->h_agree[1]) return fail(YODA_E_NCCL, "a shard did not arrive at a peer-memory exchange within 2 s");
+            }
+            return YODA_OK;
+        }
         cudaStream_t st = c->stream;
+        if (c->x_ok) CU(cudaMemcpyAsync(&c->h_agree[1], c->x_err, sizeof(u32), cudaMemcpyDeviceToHost, st));
         const bool collective = c->comm && c->fw_optimistic;
         CU(cudaMemcpyAsync(c->fw_hctl, c->fw_ctl, sizeof(FastCtl), cudaMemcpyDeviceToHost, st));
         if (collective) CU(cudaMemcpyAsync(c->h_agree, c->d_agree, sizeof(u64), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
+        if (c->x_ok && (u32)c->h_agree[1]) return fail(YODA_E_NCCL, "a shard did not arrive at a peer-memory exchange within 2 s");
         if (c->fw_optimistic) {  // the counts this evaluation ran without
             c->fw_n_classes = c->fw_hctl->n_classes;
             c->fw_n_groups = c->fw_hctl->n_groups;
@@ -1733,7 +1906,8 @@ extern "C" int yoda_comm_init(yoda_ctx *c, const void *id128, u32 rank, u32 n_ra
     NC(g_nccl.CommInitRank(&c->comm, (int)n_ranks, id, (int)rank));
     if (!c->d_agree) {
         TRY(dev_alloc(&c->d_agree, 1));
-        if (cudaMallocHost((void **)&c->h_agree, sizeof(u64)) != cudaSuccess) return fail(YODA_E_NOMEM, "cudaMallocHost of the agreement word failed");
+        if (cudaMallocHost((void **)&c->h_agree, 2 * sizeof(u64)) != cudaSuccess) return fail(YODA_E_NOMEM, "cudaMallocHost of the agreement word failed");
+        c->h_agree[0] = c->h_agree[1] = 0;  // [1]: error word of the peer-memory exchanges
     }
     return YODA_OK;
 }
