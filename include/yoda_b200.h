@@ -243,6 +243,9 @@ int64_t yoda_uint64_to_int64(uint64_t v);
 #define YODA_NCCL_ID_BYTES 128
 int yoda_comm_unique_id(void *id128);                                                    /* rank 0 */
 int yoda_comm_init(yoda_ctx *ctx, const void *id128, uint32_t rank, uint32_t n_ranks); /* all ranks */
+/* With a communicator the library runs the three per-pod exchanges of a batch itself: over NCCL by default, or -- environment
+ * YODA_B200_XCHG=peer -- with its own kernels over CUDA-IPC mapped peer memory (one process per GPU on one box; falls back
+ * to NCCL on every shard if any shard cannot map its peers).  yoda_destroy of such a context is collective. */
 
 #define YODA_XCHG_MAX 0
 #define YODA_XCHG_SUM 1
