@@ -231,6 +231,14 @@ int yoda_framework_tail(yoda_ctx *ctx, const yoda_tail_config *cfg, yoda_tail_re
 #define YODA_NOALLOC_MAX_SCORES (1u << 20)
 int yoda_normalize_scores_noalloc(const int64_t *d_scores_in, int64_t *d_scores_out, uint32_t n, void *cuda_stream);
 
+/* Host only: an Scv custom resource as JSON (the whole object, or its status alone) -> yoda_node_record; the ingest step
+ * of SURVEY.md 8(f)4.  Replaces the decoding the controller-runtime client does before y.cache.Get hands out a *scv.Scv
+ * (scheduler.go:79-80).  Fields read: status.{cardNumber, freeMemorySum, totalMemorySum, cardList[]} and per card {health,
+ * freeMemory, totalMemory, clock, core, bandwidth, power}; the Go types live in the un-vendored SCV module, so key names
+ * are matched without regard to case and unknown keys are skipped.  healthy bit g = (health == "Healthy"), as
+ * filter.go:53,57 compare.  name (may be NULL): receives metadata.name.  YODA_E_ARG: malformed JSON or no status fields;
+ * YODA_E_RANGE: more than YODA_MAX_CARDS cards (rec->n_cards holds the count). */
+int yoda_record_from_scv_json(const char *json, size_t len, yoda_node_record *rec, char *name, size_t name_cap);
 /* filter.StrToUint64 / strToUint (filter.go:60-74): strconv.Atoi, any error -> 0 */
 uint64_t yoda_parse_label(const char *s, size_t len);
 /* filter.Uint64ToInt64 (filter.go:84-86): values >= 2^63 -> 0 */

@@ -39,7 +39,7 @@ def test_kat_through_c_abi(kat, flags):
 
 @pytest.mark.parametrize("flags", PATHS)
 @pytest.mark.parametrize("adversarial", [False, True])
-@pytest.mark.parametrize("seed", range(8))
+@pytest.mark.parametrize("seed", range(24))
 def test_random_small(seed, adversarial, flags):
     rng = random.Random(77 * seed + adversarial)
     nodes = random_nodes(rng, rng.choice([1, 3, 31, 32, 33, 127, 129, 300]), adversarial)

@@ -64,6 +64,7 @@ SYMBOLS = {
     "yoda_eval_sequential": (_I, [_P, _P, _U32, _P, _P]),
     "yoda_queue_order": (_I, [_P, _P, _U32, _P]),
     "yoda_normalize_scores_noalloc": (_I, [_P, _P, _U32, _P]),
+    "yoda_record_from_scv_json": (_I, [C.c_char_p, C.c_size_t, _P, C.c_char_p, C.c_size_t]),
     "yoda_parse_label": (_U64, [C.c_char_p, C.c_size_t]),
     "yoda_uint64_to_int64": (C.c_int64, [_U64]),
     "yoda_comm_unique_id": (_I, [_P]),

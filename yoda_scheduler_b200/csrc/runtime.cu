@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <mutex>
 #include <new>
 #include <string>
@@ -1909,5 +1910,178 @@ extern "C" int yoda_comm_init(yoda_ctx *c, const void *id128, u32 rank, u32 n_ra
         if (cudaMallocHost((void **)&c->h_agree, 2 * sizeof(u64)) != cudaSuccess) return fail(YODA_E_NOMEM, "cudaMallocHost of the agreement word failed");
         c->h_agree[0] = c->h_agree[1] = 0;  // [1]: error word of the peer-memory exchanges
     }
+    return YODA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// SCV custom resource (JSON) -> yoda_node_record.  Host only.
+// The CR's Go types live in github.com/NJUPT-ISL/SCV (un-vendored, go.mod:6); what the hot path reads of them is fixed
+// by the reference's call sites: Status.{CardNumber, FreeMemorySum, TotalMemorySum, CardList[]} and
+// Card.{Health, FreeMemory, TotalMemory, Clock, Core, Bandwidth, Power}.  The JSON spelling of those names cannot be
+// checked offline, so keys are matched without regard to case ("cardList" == "CardList"); unknown keys are skipped.
+// ------------------------------------------------------------------------------------------
+namespace {
+struct JsonCur {
+    const char *p, *end;
+    void ws() { while (p < end && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r')) ++p; }
+    bool eat(char ch) { ws(); if (p < end && *p == ch) { ++p; return true; } return false; }
+};
+static bool json_string(JsonCur &c, std::string *out) {
+    if (!c.eat('"')) return false;
+    std::string s;
+    while (c.p < c.end && *c.p != '"') {
+        if (*c.p == '\\') {
+            if (++c.p >= c.end) return false;
+            switch (*c.p) {
+                case 'n': s += '\n'; break; case 't': s += '\t'; break; case 'r': s += '\r'; break; case 'b': s += '\b'; break; case 'f': s += '\f'; break;
+                case 'u': if (c.end - c.p < 5) return false; s += '?'; c.p += 4; break;  // not needed for the fields read here
+                default: s += *c.p;
+            }
+            ++c.p;
+        } else {
+            s += *c.p++;
+        }
+    }
+    if (c.p >= c.end) return false;
+    ++c.p;
+    if (out) *out = std::move(s);
+    return true;
+}
+static bool json_skip(JsonCur &c, int depth = 0);
+static bool json_uint(JsonCur &c, uint64_t *out) {  // a JSON number without sign, fraction or exponent (what encoding/json writes for uint)
+    c.ws();
+    if (c.p >= c.end || *c.p < '0' || *c.p > '9') return false;
+    unsigned __int128 v = 0;
+    while (c.p < c.end && *c.p >= '0' && *c.p <= '9') {
+        v = v * 10 + (unsigned)(*c.p++ - '0');
+        if (v > 0xFFFFFFFFFFFFFFFFull) return false;
+    }
+    if (c.p < c.end && (*c.p == '.' || *c.p == 'e' || *c.p == 'E')) return false;
+    *out = (uint64_t)v;
+    return true;
+}
+static bool json_skip(JsonCur &c, int depth) {
+    if (depth > 64) return false;
+    c.ws();
+    if (c.p >= c.end) return false;
+    if (*c.p == '"') return json_string(c, nullptr);
+    if (*c.p == '{' || *c.p == '[') {
+        const char close = *c.p == '{' ? '}' : ']';
+        const bool obj = *c.p == '{';
+        ++c.p;
+        if (c.eat(close)) return true;
+        do {
+            if (obj && (!json_string(c, nullptr) || !c.eat(':'))) return false;
+            if (!json_skip(c, depth + 1)) return false;
+        } while (c.eat(','));
+        return c.eat(close);
+    }
+    while (c.p < c.end && *c.p != ',' && *c.p != '}' && *c.p != ']' && *c.p != ' ' && *c.p != '\n' && *c.p != '\t' && *c.p != '\r') ++c.p;  // number, true, false, null
+    return true;
+}
+static bool key_is(const std::string &k, const char *name) {
+    size_t i = 0;
+    for (; i < k.size() && name[i]; ++i)
+        if (tolower((unsigned char)k[i]) != tolower((unsigned char)name[i])) return false;
+    return i == k.size() && !name[i];
+}
+// visits "key": value pairs of the object at the cursor; f returns false on a malformed value
+template <typename F>
+static bool json_object(JsonCur &c, F f) {
+    if (!c.eat('{')) return false;
+    if (c.eat('}')) return true;
+    do {
+        std::string k;
+        if (!json_string(c, &k) || !c.eat(':')) return false;
+        if (!f(k)) return false;
+    } while (c.eat(','));
+    return c.eat('}');
+}
+}  // namespace
+
+extern "C" int yoda_record_from_scv_json(const char *json, size_t len, yoda_node_record *rec, char *name, size_t name_cap) {
+    if (!json || !rec) return fail(YODA_E_ARG, "null argument");
+    memset(rec, 0, sizeof *rec);
+    if (name && name_cap) name[0] = 0;
+    bool too_many = false, saw_status_fields = false;
+    auto card = [&](JsonCur &c, uint32_t g) {
+        return json_object(c, [&](const std::string &k) {
+            uint64_t v = 0;
+            if (key_is(k, "health")) {
+                std::string h;
+                if (!json_string(c, &h)) return false;
+                if (g < YODA_MAX_CARDS && h == "Healthy") rec->healthy_mask |= 1u << g;  // filter.go:53,57: exactly this string
+                return true;
+            }
+            uint64_t *dst = nullptr;
+            if (g < YODA_MAX_CARDS) {
+                if (key_is(k, "freeMemory")) dst = &rec->free_memory[g];
+                else if (key_is(k, "totalMemory")) dst = &rec->total_memory[g];
+                else if (key_is(k, "clock")) dst = &rec->clock[g];
+                else if (key_is(k, "core")) dst = &rec->core[g];
+                else if (key_is(k, "bandwidth")) dst = &rec->bandwidth[g];
+                else if (key_is(k, "power")) dst = &rec->power[g];
+            }
+            if (!dst) return json_skip(c);
+            if (!json_uint(c, &v)) return false;
+            *dst = v;
+            return true;
+        });
+    };
+    std::function<bool(JsonCur &)> status = [&](JsonCur &c) {
+        return json_object(c, [&](const std::string &k) {
+            uint64_t v = 0;
+            if (key_is(k, "cardList")) {
+                saw_status_fields = true;
+                if (c.eat('n')) { c.p += 3; return true; }  // null: no cards
+                if (!c.eat('[')) return false;
+                uint32_t g = 0;
+                if (!c.eat(']')) {
+                    do {
+                        if (!card(c, g)) return false;
+                        ++g;
+                    } while (c.eat(','));
+                    if (!c.eat(']')) return false;
+                }
+                too_many = g > YODA_MAX_CARDS;
+                rec->n_cards = g;
+                return true;
+            }
+            uint64_t *dst = key_is(k, "cardNumber") ? &rec->card_number : key_is(k, "freeMemorySum") ? &rec->free_memory_sum
+                            : key_is(k, "totalMemorySum") ? &rec->total_memory_sum : nullptr;
+            if (!dst) return json_skip(c);
+            saw_status_fields = true;
+            if (!json_uint(c, &v)) return false;
+            *dst = v;
+            return true;
+        });
+    };
+    JsonCur c{json, json + len};
+    // either the whole object ({"metadata": {"name": ...}, "status": {...}}) or the status alone
+    const char *start = c.p;
+    bool has_status_key = false;
+    bool ok = json_object(c, [&](const std::string &k) {
+        if (key_is(k, "status")) {
+            has_status_key = true;
+            return status(c);
+        }
+        if (key_is(k, "metadata"))
+            return json_object(c, [&](const std::string &mk) {
+                if (!key_is(mk, "name")) return json_skip(c);
+                std::string n;
+                if (!json_string(c, &n)) return false;
+                if (name && name_cap) snprintf(name, name_cap, "%s", n.c_str());
+                return true;
+            });
+        return json_skip(c);
+    });
+    if (ok && !has_status_key) {
+        JsonCur d{start, json + len};
+        memset(rec, 0, sizeof *rec);
+        ok = status(d);
+    }
+    if (!ok) return fail(YODA_E_ARG, "malformed Scv JSON near offset %zu", (size_t)(c.p - json));
+    if (!saw_status_fields) return fail(YODA_E_ARG, "no Scv status fields (cardList, cardNumber, freeMemorySum, totalMemorySum) found");
+    if (too_many) return fail(YODA_E_RANGE, "the Scv lists %u cards, the device snapshot holds at most %d per node", rec->n_cards, YODA_MAX_CARDS);
     return YODA_OK;
 }
