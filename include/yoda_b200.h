@@ -144,7 +144,9 @@ int yoda_node_count(yoda_ctx *ctx, uint32_t *n_nodes); /* highest committed inde
  * whose host does not consume them -- after the exchanges every shard holds the same per-pod results, one copy is enough. */
 int yoda_eval_batch(yoda_ctx *ctx, const yoda_pod_req *pods, uint32_t n_pods, uint32_t flags, yoda_pod_result *out);
 /* same, with `d_pods` (n_pods * sizeof(yoda_pod_req)) and `d_out` (n_pods * sizeof(yoda_pod_result),
- * may be NULL) already in device memory; asynchronous on the context's stream */
+ * may be NULL) already in device memory.  Everything is queued on the context's stream; the call returns once the
+ * verdicts the kernels left on the device (which path ran, capacity overflows) have been read back -- i.e. after the
+ * batch's kernels, but without copying any results -- and has by then redone the batch if they asked for it. */
 int yoda_eval_batch_device(yoda_ctx *ctx, const void *d_pods, uint32_t n_pods, uint32_t flags, void *d_out);
 /* copy one row of the last YODA_EVAL_FULL result to the host: the O(1)-per-node memo behind
  * later Filter/Score/NormalizeScore calls of the same cycle */

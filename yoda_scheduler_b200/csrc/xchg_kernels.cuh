@@ -15,7 +15,7 @@
 // Flags carry the batch sequence number, which only grows, so nothing is ever cleared.  A shard that waits longer than
 // ~2 s gives up and raises an error word instead of hanging the GPU.
 //
-// These kernels use ordinary loads and stores on peer memory (no TMA, no multicast).
+// Peer memory is touched with ordinary loads and stores only.
 #pragma once
 #include "common.cuh"
 
