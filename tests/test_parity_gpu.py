@@ -708,3 +708,61 @@ def test_eval_without_reading_results_back():
             for k in rows:
                 assert np.array_equal(rows[k], want_rows[k][:min(n, 5)]), k
         assert np.array_equal(ctx.eval(reqs, api.EVAL_FULL), want)
+
+
+def test_single_pod_cycles_replayed_from_a_graph():
+    """The one-pod scheduling cycle is captured into a CUDA graph on its second occurrence and replayed afterwards.  The
+    replays must follow the data: different pods, a commit that changes the metrics (same node count), a node going wide,
+    and a snapshot whose class table overflows (the verdict read back after the replay sends the cycle to the exact
+    kernels).  Every cycle against the oracle, rows included."""
+    rng = np.random.default_rng(17)
+    N = 1200
+    snap = synth.make_snapshot(N)
+    labels = synth.make_pod_labels(40, 23)
+    with api.Context(N) as ctx:
+        ctx.load_snapshot(snap)
+        cl = ora.OracleCluster.from_snapshot(snap)
+
+        def cycle(lab, flags=api.EVAL_FULL, path=1):
+            res = ctx.eval(pods_to_requests(lab), flags)
+            assert ctx.timing().path == path
+            mats = ctx.fetch_all(len(lab)) if flags & api.EVAL_FULL else None
+            assert_matches_oracle(snap, lab, res, mats, o=cl.eval(lab, threads=2))
+        for k in range(8):                                   # call by call, capture, then replays
+            cycle(labels[k:k + 1])
+        for k in range(4):                                   # another key (3 pods), again captured on its second cycle
+            cycle(labels[10 + k:13 + k])
+        for k in range(4):
+            cycle(labels[20 + k:21 + k], api.EVAL_DECIDE)
+        # a metric tick: same nodes, new FreeMemory -> the cached graph must read the new snapshot
+        other = synth.make_snapshot(N, seed=synth.SEED + 4)
+        touched = rng.choice(N, N // 5, replace=False)
+        for f in ("free_memory", "healthy_mask", "free_memory_sum"):
+            getattr(snap, f)[touched] = getattr(other, f)[touched]
+        live = touched[snap.has_scv[touched] == 1]
+        ctx.upsert_many(live, snap.records(live))
+        ctx.commit()
+        cl = ora.OracleCluster.from_snapshot(snap)
+        for k in range(4):
+            cycle(labels[30 + k:31 + k])
+        # a node goes wide: another key (wide-node kernels join the sequence)
+        node = int(np.nonzero((snap.has_scv == 1) & (snap.n_cards == 8))[0][2])
+        snap.card_number[node] = np.uint64(1) << np.uint64(40)
+        ctx.upsert_many(np.array([node], np.uint32), snap.records(np.array([node])))
+        ctx.commit()
+        cl = ora.OracleCluster.from_snapshot(snap)
+        for k in range(4):
+            cycle(labels[k:k + 1])
+    # class-table overflow: every cycle ends on the exact kernels, replayed or not
+    nodes = [{"name": f"n{i}", "has_scv": True, "card_number": 2, "free_sum": 5000, "total_sum": 16000, "pods": [],
+              "cards": [{"health": "Healthy", "free": 4000 + i, "total": 8000, "clock": 30_000_000 + i, "core": 100, "bandwidth": 1 + (i % 3), "power": 50},
+                        {"health": "Healthy", "free": 1000, "total": 8000, "clock": 1000, "core": 100, "bandwidth": 2, "power": 50}]}
+             for i in range(70)]
+    snap2 = Snapshot.from_nodes(nodes)
+    with api.Context(70) as ctx:
+        ctx.load_snapshot(snap2)
+        for k in range(5):
+            lab = [{"scv/memory": str(500 + 37 * k)}]
+            res = ctx.eval(pods_to_requests(lab), api.EVAL_FULL)
+            assert ctx.timing().path == 0
+            assert_matches_oracle(snap2, lab, res, ctx.fetch_all(1))

@@ -162,6 +162,44 @@ __global__ void k_small_groups(const PodC *__restrict__ pods, u32 P, GroupDesc *
     out[p] = s;
     m_sorted[p] = s.m;
 }
+// The whole set-up of a small batch in one launch (a one-pod cycle is launch-bound): what k_pod_prep, k_init_partials,
+// k_small_groups and the clearing of the step planes and of the control block do for bigger batches.
+__global__ void k_small_setup(const yoda_pod_req *__restrict__ req, PodC *pods, u32 P, u64 *max6, u64 *count, u64 *hilo, u64 *ckey, GroupDesc *gdesc,
+                              PodS *out, u32 *m_sorted, u32 *step, FastCtl *ctl) {
+    const u32 t = threadIdx.x;
+    if (t < P * 6) {
+        step[t] = 0;
+        max6[t] = 1ull;  // collection.go:31-38
+    }
+    if (t == 0) {
+        ctl->n_groups = 0; ctl->n_classes = 0; ctl->reserved = 0; ctl->err = 0;
+    }
+    if (t >= P) return;
+    const yoda_pod_req r = req[t];
+    PodC pod;
+    pod.flags = r.flags & 7u;
+    pod.num = (r.flags & YODA_POD_HAS_NUMBER) ? r.number : 1ull;  // filter.go:11-16
+    pod.mem = (r.flags & YODA_POD_HAS_MEMORY) ? r.memory : 0ull;  // filter.go:18-33
+    pod.clk = (r.flags & YODA_POD_HAS_CLOCK) ? r.clock : 0ull;    // filter.go:35-50
+    pod.pad = 0;
+    pods[t] = pod;
+    count[t] = 0; hilo[2 * t] = 0; hilo[2 * t + 1] = 0; ckey[t] = 0;
+    u32 n32, c32, gf;
+    group_key(pod, n32, c32, gf);
+    GroupDesc g;
+    g.flags = gf; g.c = c32; g.num = n32; g.seg_start = t; g.seg_end = t + 1; g.pad0 = g.pad1 = g.pad2 = 0;
+    gdesc[t] = g;
+    PodS ps;
+    ps.m = clamp32(pod.mem);
+    ps.c = (pod.flags & YODA_POD_HAS_CLOCK) ? clamp32(pod.clk) : 0u;
+    ps.num = clamp32(pod.num);
+    const u32 rq = min(ps.num, 255u);
+    ps.req = ((pod.flags & YODA_POD_HAS_MEMORY) ? rq : 0u) | (((pod.flags & YODA_POD_HAS_CLOCK) ? rq : 0u) << 8) | (pod.flags << 16);
+    ps.cls = t; ps.orig = t; ps.gid = t; ps.pad = 0;
+    out[t] = ps;
+    m_sorted[t] = ps.m;
+}
+
 __global__ void k_small_classes(u32 P, const u64 *__restrict__ max6, u32 *cls_max, FastCtl *ctl) {
     const u32 t = threadIdx.x;
     if (t >= P * 6) return;

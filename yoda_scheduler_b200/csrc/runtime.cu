@@ -197,6 +197,25 @@ struct yoda_ctx {
     u64 *sq_alloc = nullptr;
     u32 *sq_stat = nullptr, *sq_pos = nullptr, *sq_order = nullptr, *sq_status = nullptr;
     u32 sq_pods_cap = 0;
+    // CUDA graph of the small-batch sequence (<= FAST_SMALL_P pods through yoda_eval_batch: the one-pod scheduling cycle).
+    // A cycle is ~10 short kernels, 3 copies and 2 memsets -- launch-bound -- and identical from cycle to cycle until the
+    // node count changes, so the second cycle with the same key captures the sequence and later ones replay it.
+    struct GraphKey {
+        // everything the host decides grids and kernel arguments from; the snapshot's DATA may change (commits), its buffers do not move
+        u32 P = 0, flags = 0, n_nodes = 0, n_wide = 0;
+        cudaStream_t stream = nullptr;
+        bool operator==(const GraphKey &o) const { return P == o.P && flags == o.flags && n_nodes == o.n_nodes && n_wide == o.n_wide && stream == o.stream; }
+    };
+    struct GraphPost {  // what the host-side state looks like after the sequence was enqueued
+        int ph_path = 0, ph_done = -1;
+        bool fw_small = false, fw_deferred_err = false, fw_decide_merged = false, res_raw32 = false, last_full = false;
+        u32 last_P = 0, fw_n_groups = 0, fw_n_classes = 0, launches = 0;
+    };
+    GraphKey g_key{}, g_seen{};
+    GraphPost g_post{};
+    cudaGraphExec_t g_exec = nullptr;
+    bool g_capturing = false, g_enabled = true;
+    bool g_replayed = false;  // the last evaluation was a graph replay: only its total time was measured
     u32 score_slots = 0, out_slots = 0;  // CTAs of the hot kernels resident on the device at once
     u32 last_score_chunk = 0, last_out_chunk = 0;  // pods per CTA the hot kernels of the last evaluation ran with (yoda_debug_pod_order)
     int n_sms = 0;  // DECIDE on one GPU: the score pass also yields counts and the node choice
@@ -266,6 +285,10 @@ extern "C" int yoda_create(const yoda_config *cfg, yoda_ctx **out) {
     if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess)
         return bail(fail(YODA_E_CUDA, "cudaStreamCreate failed"));
     c->stream = c->own_stream;
+    {
+        const char *g = getenv("YODA_B200_GRAPH");  // YODA_B200_GRAPH=0: never capture
+        c->g_enabled = !(g && g[0] == '0');
+    }
     if (cudaDeviceGetAttribute(&c->n_sms, cudaDevAttrMultiProcessorCount, cfg->device) != cudaSuccess || c->n_sms <= 0) c->n_sms = 148;
     {
         int per_sm = 0;
@@ -361,6 +384,7 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     dev_free(s.cardnum32); dev_free(s.stat32); dev_free(s.tk32); dev_free(s.order); dev_free(s.order_key);
     dev_free(c->ord_keys_out); dev_free(c->ord_iota);
     if (c->ord_tmp) cudaFree(c->ord_tmp);
+    if (c->g_exec) cudaGraphExecDestroy(c->g_exec);
     dev_free(c->d_wide_list); dev_free(c->d_wide_cnt);
     dev_free(c->tl_tilecnt); dev_free(c->tl_out); dev_free(c->tl_other);
     dev_free(c->d_wide_flag); dev_free(c->d_lohi); dev_free(c->d_list); dev_free(c->d_upd);
@@ -604,6 +628,13 @@ static int ensure_matrices(yoda_ctx *c, u32 P, u64 stride, u32 raw_elem_bytes) {
     return YODA_OK;
 }
 
+// phase events; not while the small-batch sequence is being captured into a graph (see yoda_eval_batch)
+static int ev_record(yoda_ctx *c, int which) {
+    if (c->g_capturing) return YODA_OK;
+    CU(cudaEventRecord(c->ev[which], c->stream));
+    return YODA_OK;
+}
+
 #define LAUNCHED(c)          \
     do {                     \
         CU(cudaGetLastError()); \
@@ -768,14 +799,10 @@ static int fast_phase0(yoda_ctx *c) {
     const u32 P = c->ph_P, N = c->snap.n_nodes;
     cudaStream_t st = c->stream;
     const u32 pb = (P + 255) / 256;
-    CU(cudaMemsetAsync(c->fw_ctl, 0, sizeof(FastCtl), st));
-    c->fw_small = P <= FAST_SMALL_P && P <= fast_class_cap(c);
-    if (c->fw_small) {  // one pod = one group = one class: no hashing, no sort, no host round trip
-        k_small_groups<<<1, 32, 0, st>>>(c->d_pods, P, c->fw_gdesc, c->fw_pods, c->fw_m_sorted);
-        LAUNCHED(c);
+    if (!c->fw_small) CU(cudaMemsetAsync(c->fw_ctl, 0, sizeof(FastCtl), st));
+    if (c->fw_small) {  // one pod = one group = one class: no hashing, no sort, no host round trip; set up by k_small_setup (phase0)
         c->fw_n_groups = P;
-        CU(cudaEventRecord(c->ev[EV_PREP], st));
-        CU(cudaMemsetAsync(c->fw_step, 0, (size_t)P * 6 * sizeof(u32), st));
+        TRY(ev_record(c, EV_PREP));
         if (N) {
             k_max_thresholds<<<dim3((N + MAXT - 1) / MAXT, 1), MAXT, 0, st>>>(c->snap, c->fw_gdesc, P, nullptr, c->fw_m_sorted, c->fw_step, P);
             LAUNCHED(c);
@@ -815,7 +842,7 @@ static int fast_phase0(yoda_ctx *c) {
     k_build_sorted<<<pb, 256, 0, st>>>(c->d_pods, P, c->fw_keys_out, c->fw_vals_out, c->fw_gdesc, FAST_GROUP_CAP, c->fw_pods,
                                        c->fw_m_sorted);
     LAUNCHED(c);
-    CU(cudaEventRecord(c->ev[EV_PREP], st));
+    TRY(ev_record(c, EV_PREP));
     CU(cudaMemsetAsync(c->fw_step, 0, (size_t)P * 6 * sizeof(u32), st));
     if (N) {
         // eight groups per CTA pass: the per-node setup (loads, k-th largest FreeMemory) costs about as much as one group
@@ -997,18 +1024,25 @@ static int phase0(yoda_ctx *c, const yoda_pod_req *d_req) {
     const u32 P = c->ph_P;
     cudaStream_t st = c->stream;
     c->launches = 0;
-    CU(cudaEventRecord(c->ev[EV_START], st));
-    k_pod_prep<<<(P + 255) / 256, 256, 0, st>>>(d_req, c->d_pods, P);
-    LAUNCHED(c);
-    k_init_partials<<<(P + 255) / 256, 256, 0, st>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, P);
-    LAUNCHED(c);
+    TRY(ev_record(c, EV_START));
+    c->fw_small = c->ph_path == 1 && P <= FAST_SMALL_P && P <= fast_class_cap(c);
+    if (c->fw_small) {
+        k_small_setup<<<1, 64, 0, st>>>(d_req, c->d_pods, P, c->d_max6, c->d_count, c->d_hilo, c->d_ckey, c->fw_gdesc, c->fw_pods, c->fw_m_sorted, c->fw_step,
+                                        c->fw_ctl);
+        LAUNCHED(c);
+    } else {
+        k_pod_prep<<<(P + 255) / 256, 256, 0, st>>>(d_req, c->d_pods, P);
+        LAUNCHED(c);
+        k_init_partials<<<(P + 255) / 256, 256, 0, st>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, P);
+        LAUNCHED(c);
+    }
     if (c->ph_path == 1) TRY(fast_phase0(c));
     if (c->ph_path == 1) TRY(wide_pods_launch(c, 0));  // after k_max_scan, which stores the table nodes' maxima
     if (c->ph_path == 0) {
-        CU(cudaEventRecord(c->ev[EV_PREP], st));
+        TRY(ev_record(c, EV_PREP));
         TRY(direct_pods_launch(c, 0));
     }
-    CU(cudaEventRecord(c->ev[EV_MAX], st));
+    TRY(ev_record(c, EV_MAX));
     return YODA_OK;
 }
 
@@ -1034,7 +1068,7 @@ static int phase1(yoda_ctx *c) {
         if (c->fw_gated) TRY(direct_pods_launch(c, 1, true));
     }
     if (c->ph_path == 0) TRY(direct_pods_launch(c, 1));
-    CU(cudaEventRecord(c->ev[EV_SCORE], c->stream));
+    TRY(ev_record(c, EV_SCORE));
     return YODA_OK;
 }
 
@@ -1055,7 +1089,7 @@ static int phase3(yoda_ctx *c) {
     k_finalize<<<(P + 255) / 256, 256, 0, c->stream>>>(c->d_max6, c->d_count, c->d_hilo, c->d_ckey, c->d_res, P,
                                                        c->ph_path == 1 && c->fw_decide_merged);
     LAUNCHED(c);
-    CU(cudaEventRecord(c->ev[EV_WRITE], c->stream));
+    TRY(ev_record(c, EV_WRITE));
     return YODA_OK;
 }
 
@@ -1078,6 +1112,7 @@ static int begin_locked(yoda_ctx *c, u32 P, u32 flags) {
     c->fw_defer_groups = false;
     c->fw_opt_ok = false;
     c->fw_optimistic = false;
+    c->g_replayed = false;
     c->ph_done = -1;
     c->last_P = 0;
     c->last_full = false;
@@ -1239,6 +1274,14 @@ static void collect_timing(yoda_ctx *c, bool copies) {
     yoda_timing &t = c->timing;
     memset(&t, 0, sizeof t);
     cudaEventElapsedTime(&t.total_ms, c->ev[EV_START], c->ev[EV_WRITE]);
+    if (c->g_replayed) {  // one graph launch: the phases were not timed apart
+        t.kernels = c->launches;
+        t.path = (u32)c->ph_path;
+        t.n_classes = c->fw_n_classes;
+        t.n_groups = c->fw_n_groups;
+        cudaGetLastError();
+        return;
+    }
     cudaEventElapsedTime(&t.prep_ms, c->ev[EV_START], c->ev[EV_PREP]);
     cudaEventElapsedTime(&t.max_ms, c->ev[EV_PREP], c->ev[EV_MAX]);
     cudaEventElapsedTime(&t.score_ms, c->ev[EV_MAX], c->ev[EV_SCORE]);
@@ -1386,6 +1429,59 @@ extern "C" int yoda_eval_batch(yoda_ctx *c, const yoda_pod_req *pods, u32 P, u32
     cudaStream_t st = c->stream;
     const bool staged = P <= STAGE_PODS;  // small batches: one cheap host copy buys truly asynchronous DMA
     if (staged) memcpy(c->h_req, pods, (size_t)P * sizeof(yoda_pod_req));
+    // ---- the one-pod scheduling cycle (and its <= 8-pod siblings) as a CUDA graph -----------------------------------
+    if (c->g_enabled && !c->comm && c->ph_path == 1 && out && P <= FAST_SMALL_P && P <= c->fw_tables_classes && c->fw_ctl) {
+        const yoda_ctx::GraphKey key{P, flags, c->snap.n_nodes, c->n_wide, st};
+        if (!(c->g_exec && key == c->g_key) && key == c->g_seen) {
+            // second cycle with this key (the first one ran call by call and left every buffer at its final size): capture
+            if (c->g_exec) cudaGraphExecDestroy(c->g_exec);
+            c->g_exec = nullptr;
+            cudaGraph_t graph = nullptr;
+            CU(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            c->g_capturing = true;
+            int rc = YODA_OK;
+            if (cudaMemcpyAsync(c->d_req, c->h_req, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = YODA_E_CUDA;
+            if (!rc) rc = run_all_locked(c, c->d_req);
+            if (!rc && (cudaMemcpyAsync(c->h_res, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+                        cudaMemcpyAsync(c->fw_hctl, c->fw_ctl, sizeof(FastCtl), cudaMemcpyDeviceToHost, st) != cudaSuccess))  // results and verdict ride in the graph
+                rc = YODA_E_CUDA;
+            c->g_capturing = false;
+            const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+            if (!rc && ce == cudaSuccess && graph && cudaGraphInstantiate(&c->g_exec, graph, 0) == cudaSuccess) {
+                c->g_key = key;
+                c->g_post = yoda_ctx::GraphPost{c->ph_path, c->ph_done, c->fw_small, c->fw_deferred_err, c->fw_decide_merged, c->res_raw32, c->last_full,
+                                                c->last_P, c->fw_n_groups, c->fw_n_classes, c->launches};
+            } else {
+                c->g_exec = nullptr;
+                c->g_enabled = false;  // this driver / sequence cannot be captured: call by call from now on
+                cudaGetLastError();
+                TRY(begin_locked(c, P, flags));
+            }
+            if (graph) cudaGraphDestroy(graph);
+        }
+        if (c->g_exec && key == c->g_key) {
+            const yoda_ctx::GraphPost &gp = c->g_post;
+            CU(cudaEventRecord(c->ev[EV_START], st));
+            CU(cudaGraphLaunch(c->g_exec, st));
+            CU(cudaEventRecord(c->ev[EV_WRITE], st));  // only the total is timed: copies included, no phase split
+            c->g_replayed = true;
+            c->ph_path = gp.ph_path; c->ph_done = gp.ph_done; c->fw_small = gp.fw_small; c->fw_deferred_err = gp.fw_deferred_err;
+            c->fw_decide_merged = gp.fw_decide_merged; c->res_raw32 = gp.res_raw32; c->last_full = gp.last_full; c->last_P = gp.last_P;
+            c->fw_n_groups = gp.fw_n_groups; c->fw_n_classes = gp.fw_n_classes; c->launches = gp.launches;
+            CU(cudaStreamSynchronize(st));
+            c->fw_deferred_err = false;
+            if (c->fw_hctl->err) {  // the class tables do not fit the packed format: the cycle again with the exact kernels
+                c->g_replayed = false;
+                TRY(redo_direct_if_flagged(c, c->d_req, c->fw_hctl->err));
+                CU(cudaMemcpyAsync(c->h_res, c->d_res, (size_t)P * sizeof(yoda_pod_result), cudaMemcpyDeviceToHost, st));
+                CU(cudaStreamSynchronize(st));
+            }
+            memcpy(out, c->h_res, (size_t)P * sizeof(yoda_pod_result));
+            collect_timing(c, true);
+            return YODA_OK;
+        }
+        c->g_seen = key;
+    }
     CU(cudaEventRecord(c->ev[EV_H2D0], st));
     CU(cudaMemcpyAsync(c->d_req, staged ? c->h_req : pods, (size_t)P * sizeof(yoda_pod_req), cudaMemcpyHostToDevice, st));
     CU(cudaEventRecord(c->ev[EV_H2D1], st));
@@ -1458,7 +1554,7 @@ extern "C" int yoda_eval_sequential(yoda_ctx *c, const yoda_pod_req *pods, u32 P
     if (c->ph_path == 1) TRY(fast_classes(c));
     if (c->ph_path != 1)
         return fail(YODA_E_RANGE, "sequential-commit evaluation needs the table path (too many requirement groups or classes in this batch)");
-    CU(cudaEventRecord(c->ev[EV_SCORE], st));
+    TRY(ev_record(c, EV_SCORE));
     const u32 N = c->snap.n_nodes;
     if (N) {
         k_seq_positions<<<(P + 255) / 256, 256, 0, st>>>(c->fw_pods, P, c->sq_pos);
