@@ -745,6 +745,12 @@ def test_single_pod_cycles_replayed_from_a_graph():
         cl = ora.OracleCluster.from_snapshot(snap)
         for k in range(4):
             cycle(labels[30 + k:31 + k])
+        # a big FULL batch in between reallocates pod buffers, matrices and class tables: the cached graph must not survive it
+        big = synth.make_pod_labels(6000, 29)
+        res = ctx.eval(pods_to_requests(big), api.EVAL_FULL)
+        assert_matches_oracle(snap, big, res, None, o=cl.eval(big, threads=8, full=False))
+        for k in range(4):
+            cycle(labels[k:k + 1])
         # a node goes wide: another key (wide-node kernels join the sequence)
         node = int(np.nonzero((snap.has_scv == 1) & (snap.n_cards == 8))[0][2])
         snap.card_number[node] = np.uint64(1) << np.uint64(40)

@@ -2,10 +2,10 @@ import time, numpy as np, sys
 sys.path.insert(0, '/root/repo')
 from yoda_scheduler_b200 import api, synth
 snap = synth.make_snapshot(50000)
-reqs = synth.make_requests(64, 5)
+reqs = synth.make_requests(20000, 5)
 with api.Context(50000) as ctx:
     ctx.load_snapshot(snap)
-    for P in (1, 8, 9, 64):
+    for P in [int(a) for a in sys.argv[1:]] or (1, 8, 9, 64):
         for flags in (api.EVAL_FULL, api.EVAL_DECIDE):
             r = np.ascontiguousarray(reqs[:P]); ts = []; dev = []
             for i in range(300):

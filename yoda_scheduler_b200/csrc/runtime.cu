@@ -573,10 +573,19 @@ extern "C" int yoda_node_count(yoda_ctx *c, u32 *n) {
 // ------------------------------------------------------------------------------------------
 // evaluation
 // ------------------------------------------------------------------------------------------
+// The captured small-batch graph holds device addresses: whenever a buffer it may reference is reallocated, it goes.
+static void graph_drop(yoda_ctx *c) {
+    if (c->g_exec) cudaGraphExecDestroy(c->g_exec);
+    c->g_exec = nullptr;
+    c->g_key = yoda_ctx::GraphKey{};
+    c->g_seen = yoda_ctx::GraphKey{};
+}
+
 static int ensure_pods(yoda_ctx *c, u32 P) {
     if (P <= c->pods_cap) return YODA_OK;
     const u32 cap = round_up(std::max(P, 1024u), 1024);
     CU(cudaStreamSynchronize(c->stream));
+    graph_drop(c);
     dev_free(c->d_req); dev_free(c->d_pods); dev_free(c->d_max6); dev_free(c->d_count);
     dev_free(c->d_hilo); dev_free(c->d_ckey); dev_free(c->d_res);
     if (c->h_req) cudaFreeHost(c->h_req);
@@ -601,6 +610,7 @@ static int ensure_pods(yoda_ctx *c, u32 P) {
 static int ensure_raw(yoda_ctx *c, size_t bytes) {
     if (bytes <= c->raw_cap) return YODA_OK;
     CU(cudaStreamSynchronize(c->stream));
+    graph_drop(c);
     dev_free(c->d_raw);
     c->raw_cap = 0;
     TRY(dev_alloc((u8 **)&c->d_raw, bytes));
@@ -613,6 +623,7 @@ static int ensure_matrices(yoda_ctx *c, u32 P, u64 stride, u32 raw_elem_bytes) {
     TRY(ensure_raw(c, need * raw_elem_bytes));
     if (need > c->norm_cap) {
         CU(cudaStreamSynchronize(c->stream));
+        graph_drop(c);
         dev_free(c->d_norm);
         c->norm_cap = 0;
         TRY(dev_alloc(&c->d_norm, need));
@@ -620,6 +631,7 @@ static int ensure_matrices(yoda_ctx *c, u32 P, u64 stride, u32 raw_elem_bytes) {
     }
     if (need_bits > c->bits_cap) {
         CU(cudaStreamSynchronize(c->stream));
+        graph_drop(c);
         dev_free(c->d_bits);
         c->bits_cap = 0;
         TRY(dev_alloc(&c->d_bits, need_bits));
@@ -656,6 +668,7 @@ static int ensure_fast(yoda_ctx *c, u32 P) {
     }
     if (P <= c->fw_pods_cap) return YODA_OK;
     CU(cudaStreamSynchronize(c->stream));
+    graph_drop(c);
     const u32 cap = c->pods_cap;  // grown by ensure_pods just before
     u32 htab = 1024;
     while (htab < 2 * cap) htab <<= 1;
@@ -920,6 +933,7 @@ static int fast_classes(yoda_ctx *c) {
         c->fw_n_classes = P;
         if (c->fw_n_classes > c->fw_tables_classes) {
             CU(cudaStreamSynchronize(st));
+            graph_drop(c);
             dev_free(c->fw_tables);
             c->fw_tables_classes = 0;
             const u32 want = std::min(ccap, 64u);
@@ -991,6 +1005,7 @@ static int fast_classes(yoda_ctx *c) {
         return YODA_OK;
     }
     if (c->fw_n_classes > c->fw_tables_classes) {
+        graph_drop(c);
         dev_free(c->fw_tables);
         c->fw_tables_classes = 0;
         const u32 want = std::min(ccap, std::max(c->fw_n_classes * 2, 64u));
