@@ -405,6 +405,43 @@ def test_class_tables_plain_division_branches(n_pods):
     assert_matches_oracle(snap, labels, res, mats)
 
 
+def test_class_tables_families_and_plain_classes_interleaved():
+    """The class tables are computed family by family: classes sorted by their maxima, quotients and admission
+    bits carried from one class to the next and recomputed only for the maxima that change.  Four card models
+    make families that differ in every divisor; inside a family the classes differ in MaxFreeMemory only, in
+    MaxClock only (the D nodes), or in both; and the pods that ask for clock 1200 see only the B cards, whose
+    power is 1 -- a plain-division class that sorts into the middle of the walk, between reciprocal-path classes."""
+    rng = random.Random(77)
+    models = {"A": dict(bandwidth=100, clock=800, core=1, power=200, total=10000),
+              "B": dict(bandwidth=500, clock=1200, core=4000, power=1, total=20000),
+              "C": dict(bandwidth=900, clock=1000, core=6000, power=300, total=40000),
+              "D": dict(bandwidth=300, clock=900, core=5000, power=250, total=80000)}
+    nodes = []
+    for i in range(240):
+        kind = "ABCD"[i % 4]
+        m = dict(models[kind])
+        if kind == "D":
+            m["clock"] = 900 + 10 * (i % 7)     # MaxClock moves with the feasible set while the other maxima stay
+        nc = rng.choice([2, 4, 8])
+        cards = [{"health": "Healthy" if rng.random() > 0.1 else "Unhealthy", "free": rng.randrange(m["total"] + 1), **m} for _ in range(nc)]
+        nodes.append({"name": f"n{i}", "has_scv": True, "card_number": nc, "cards": cards, "free_sum": sum(c["free"] for c in cards),
+                      "total_sum": nc * m["total"], "pods": []})
+    labels = []
+    for k in range(400):
+        top = rng.choice([10000, 20000, 40000, 80000])
+        d = {"scv/memory": str(rng.randrange(top // 2, top)), "scv/number": str(rng.choice([1, 1, 2, 3, 4]))}
+        if k % 5 == 0:
+            d["scv/clock"] = str(rng.choice([1200, 1000, 940, 920]))
+        labels.append(d)
+    snap = Snapshot.from_nodes(nodes)
+    res, mats, t = gpu_cycle(snap, pods_to_requests(labels), api.EVAL_FULL)
+    assert t.path == 1 and t.n_classes >= 15, (t.path, t.n_classes)
+    o = assert_matches_oracle(snap, labels, res, mats, what="class families")
+    maxima = np.unique(np.stack([res[k] for k in ("max_bandwidth", "max_clock", "max_core", "max_free_memory", "max_power", "max_total_memory")], axis=1), axis=0)
+    plain = maxima[(maxima <= 1).any(axis=1) & (maxima[:, 0] > 1)]
+    assert len(plain) >= 2, "expected plain-division classes with a bandwidth maximum above 1 (they sort between the families)"
+
+
 def test_maxima_scan_across_tiles():
     """Requirement groups much longer than one scan tile (1024 pods), groups that start and end inside a
     tile, and a tail of one-pod groups: the maxima of every pod against the oracle."""

@@ -479,7 +479,7 @@ __global__ void k_cap_flag(const FastCtl *__restrict__ ctl, u64 *flag) { *flag =
 // With a in 32 bits that is one 32x32 high product and one 32x32+64 multiply-add.  Nodes with a field
 // >= 2^32/100 and classes with a maximum of 1 (no 64-bit reciprocal) take the plain-division path.
 #define CLST 128
-#define CLS_PER 4  // classes per thread: the node's 48 field values are loaded once and reused
+#define CLS_PER 8  // classes per thread: the node's 48 field values are loaded once, and quotients are reused between classes
 
 __device__ __forceinline__ u32 rdiv(u32 a, u32 Mhi, u32 Mlo) {
     return (u32)(((u64)a * Mhi + __umulhi(a, Mlo)) >> 32);  // a*Mhi + carry < 2^64
@@ -498,33 +498,85 @@ __device__ __forceinline__ u32 card_score_plain(const DevSnap &s, u32 n, int g, 
     return ((u32)cs & CS_SCORE_MASK) | (((q0 | q1 | q2 | q3 | q4 | q5 | cs) >= CS_LIMIT) ? 0x80000000u : 0u);
 }
 
+// Classes in the order the table kernel walks them: sorted by (bandwidth, core, power, total, clock, free) maxima, so that
+// classes of one "family" -- the same best card model, i.e. equal maxima except for MaxFreeMemory, which is what
+// distinguishes most classes of a real batch -- sit next to each other and share five of their six quotients.
+// Rank by counting (n <= 4096 classes, usually < 100); order[rank] = class id.
+// One warp per class, the lanes stride over the other classes.
+#define CLS_ORDER_T 128
+__global__ void __launch_bounds__(CLS_ORDER_T) k_class_order(const u32 *__restrict__ cls_max, u32 n_classes, const FastCtl *__restrict__ ctl,
+                                                             bool count_on_device, u32 *order) {
+    if (count_on_device) n_classes = min(n_classes, ctl->n_classes);
+    const u32 i = (blockIdx.x * CLS_ORDER_T + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i >= n_classes) return;  // warp-uniform
+    constexpr int key[6] = {0, 2, 4, 5, 1, 3};  // cls_max order is bw, clock, core, free, power, total
+    u32 mine[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) mine[k] = cls_max[i * 6 + key[k]];
+    u32 rank = 0;
+    for (u32 j = lane; j < n_classes; j += 32) {
+        bool lt = false, eq = true;  // class j before class i / equal so far
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const u32 o = cls_max[j * 6 + key[k]];
+            lt = lt || (eq && o < mine[k]);
+            eq = eq && o == mine[k];
+        }
+        rank += (lt || (eq && j < i)) ? 1u : 0u;  // the tuples are distinct; the index settles whatever is left
+    }
+    rank = __reduce_add_sync(0xFFFFFFFFu, rank);
+    if (lane == 0) order[rank] = i;
+}
+
 struct ClassConsts {
     u32 d[6];     // maxima in cls_max order
     u32 d100[6];  // min(100 * d, 2^32 - 1): a <= d100 <=> x <= d for every a = 100x < 2^32
     u32 mhi[6], mlo[6];
     u32 plain;    // some maximum is 1
+    u32 cid;      // the class this slot of the block computes
+    u32 chg;      // bit f: maximum f differs from the previous reciprocal-path class of the block (all set for the first)
 };
+#define CLS_CHG_FAMILY 0x35u  // bandwidth, core, power, total: the divisors of five of the six quotients
+#define CLS_CHG_CLOCK 0x02u   // MaxClock only gates (algorithm.go:60 divides the clock by MaxBandwidth)
+#define CLS_CHG_FREE 0x08u
 
+// order: the walk order (k_class_order), nullptr = class ids as they are (small batches: a class per pod).
 // count_on_device: the class count is taken from ctl (the host sized the grid for the table capacity instead of
 // reading the count back); surplus blocks leave at once.
 __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__restrict__ cls_max, u32 n_classes, u32 *tables,
-                                                       FastCtl *ctl, bool count_on_device) {
+                                                       FastCtl *ctl, bool count_on_device, const u32 *__restrict__ order) {
     __shared__ ClassConsts cc[CLS_PER];
     if (count_on_device) n_classes = min(n_classes, ctl->n_classes);
-    const u32 cid0 = blockIdx.y * CLS_PER;
-    if (cid0 >= n_classes) return;
-    const u32 ncls = min((u32)CLS_PER, n_classes - cid0);
-    if (threadIdx.x < CLS_PER) cc[threadIdx.x].plain = 0;
+    const u32 pos0 = blockIdx.y * CLS_PER;
+    if (pos0 >= n_classes) return;
+    const u32 ncls = min((u32)CLS_PER, n_classes - pos0);
+    if (threadIdx.x < CLS_PER) {
+        cc[threadIdx.x].plain = 0;
+        cc[threadIdx.x].cid = threadIdx.x < ncls ? (order ? order[pos0 + threadIdx.x] : pos0 + threadIdx.x) : 0u;
+    }
     __syncthreads();
     if (threadIdx.x < ncls * 6) {
         const u32 k = threadIdx.x / 6, f = threadIdx.x % 6;
-        const u32 d = cls_max[cid0 * 6 + threadIdx.x];
+        const u32 d = cls_max[cc[k].cid * 6 + f];
         const u64 M = d > 1 ? (0xFFFFFFFFFFFFFFFFull / d) + 1ull : 0ull;  // ceil(2^64 / d), also for powers of two
         cc[k].d[f] = d;
         cc[k].d100[f] = (u32)min((u64)d * 100ull, 0xFFFFFFFFull);
         cc[k].mhi[f] = (u32)(M >> 32);
         cc[k].mlo[f] = (u32)M;
-        if (d <= 1) cc[k].plain = 1;
+        if (d <= 1) atomicOr(&cc[k].plain, 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {  // which maxima change from one reciprocal-path class of the block to the next
+        int prev = -1;
+        for (u32 k = 0; k < ncls; ++k) {
+            u32 chg = 0x3Fu;
+            if (prev >= 0) {
+                chg = 0;
+                for (int f = 0; f < 6; ++f) chg |= (cc[k].d[f] != cc[prev].d[f]) ? (1u << f) : 0u;
+            }
+            cc[k].chg = chg;
+            if (!cc[k].plain) prev = (int)k;
+        }
     }
     __syncthreads();
     const u32 n = blockIdx.x * CLST + threadIdx.x;
@@ -532,7 +584,7 @@ __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__r
     const u32 meta = s.meta[n];
     if (meta & META_WIDE) {  // scored by the exact kernels; its narrow planes are truncations, keep them out of the tables
         for (u32 k = 0; k < ncls; ++k) {
-            uint4 *dst = reinterpret_cast<uint4 *>(tables + ((size_t)(cid0 + k) * s.cap + n) * G);
+            uint4 *dst = reinterpret_cast<uint4 *>(tables + ((size_t)cc[k].cid * s.cap + n) * G);
             dst[0] = make_uint4(0, 0, 0, 0);
             dst[1] = make_uint4(0, 0, 0, 0);
         }
@@ -554,6 +606,9 @@ __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__r
         }
     }
     bool big = false;
+    // carried from class to class (a thread on the plain path never reads them):
+    u32 fam_sum[G], fam_or[G], q_free[G];  // bw + clock + core + power + total quotients, their OR, the FreeMemory quotient
+    u32 adm_fam = 0, adm_clock = 0, adm_free = 0;  // bit g: card g within the class maxima of those fields
     for (u32 k = 0; k < ncls; ++k) {
         const ClassConsts &c = cc[k];
         u32 out[G];
@@ -568,19 +623,43 @@ __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__r
                     if (h == g) out[h] = w;
             }
         } else {
+            const u32 chg = c.chg;  // block-uniform
+            if (chg & CLS_CHG_FAMILY) {
+                adm_fam = 0;
+#pragma unroll
+                for (int g = 0; g < G; ++g) {
+                    const u32 q0 = rdiv(a[F_BW][g], c.mhi[0], c.mlo[0]), q1 = rdiv(a[F_CLOCK][g], c.mhi[0], c.mlo[0]),
+                              q2 = rdiv(a[F_CORE][g], c.mhi[2], c.mlo[2]), q3 = rdiv(a[F_POWER][g], c.mhi[4], c.mlo[4]),
+                              q5 = rdiv(a[F_TOTAL][g], c.mhi[5], c.mlo[5]);
+                    fam_sum[g] = q0 + q1 + q2 + q3 + q5;
+                    fam_or[g] = q0 | q1 | q2 | q3 | q5;
+                    const bool in = a[F_BW][g] <= c.d100[0] && a[F_CORE][g] <= c.d100[2] && a[F_POWER][g] <= c.d100[4] && a[F_TOTAL][g] <= c.d100[5];
+                    adm_fam |= in ? (1u << g) : 0u;
+                }
+            }
+            if (chg & CLS_CHG_CLOCK) {
+                adm_clock = 0;
+#pragma unroll
+                for (int g = 0; g < G; ++g) adm_clock |= (a[F_CLOCK][g] <= c.d100[1]) ? (1u << g) : 0u;
+            }
+            if (chg & CLS_CHG_FREE) {
+                adm_free = 0;
+#pragma unroll
+                for (int g = 0; g < G; ++g) {
+                    q_free[g] = rdiv(a[F_FREE][g], c.mhi[3], c.mlo[3]);
+                    adm_free |= (a[F_FREE][g] <= c.d100[3]) ? (1u << g) : 0u;
+                }
+            }
+            const u32 adm = adm_fam & adm_clock & adm_free;
 #pragma unroll
             for (int g = 0; g < G; ++g) {
-                const bool adm = a[F_BW][g] <= c.d100[0] && a[F_CLOCK][g] <= c.d100[1] && a[F_CORE][g] <= c.d100[2] &&
-                                 a[F_FREE][g] <= c.d100[3] && a[F_POWER][g] <= c.d100[4] && a[F_TOTAL][g] <= c.d100[5];
-                const u32 q0 = rdiv(a[F_BW][g], c.mhi[0], c.mlo[0]), q1 = rdiv(a[F_CLOCK][g], c.mhi[0], c.mlo[0]),
-                          q2 = rdiv(a[F_CORE][g], c.mhi[2], c.mlo[2]), q3 = rdiv(a[F_POWER][g], c.mhi[4], c.mlo[4]),
-                          q4 = rdiv(a[F_FREE][g], c.mhi[3], c.mlo[3]), q5 = rdiv(a[F_TOTAL][g], c.mhi[5], c.mlo[5]);
-                const u32 cs = q0 + q1 + q2 + q3 + q4 * 2u + q5;  // exact when every term < CS_LIMIT, flagged otherwise
-                big |= adm && ((q0 | q1 | q2 | q3 | q4 | q5 | cs) >= CS_LIMIT);
-                out[g] = (adm ? (cs & CS_SCORE_MASK) : 0u) | (((hm >> g) & 1u) << CS_HEALTH_SHIFT);
+                const u32 cs = fam_sum[g] + q_free[g] * 2u;  // exact when every term < CS_LIMIT, flagged otherwise
+                const bool ad = (adm >> g) & 1u;
+                big |= ad && ((fam_or[g] | q_free[g] | cs) >= CS_LIMIT);
+                out[g] = (ad ? (cs & CS_SCORE_MASK) : 0u) | (((hm >> g) & 1u) << CS_HEALTH_SHIFT);
             }
         }
-        uint4 *dst = reinterpret_cast<uint4 *>(tables + ((size_t)(cid0 + k) * s.cap + n) * G);
+        uint4 *dst = reinterpret_cast<uint4 *>(tables + ((size_t)c.cid * s.cap + n) * G);
         dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
         dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
     }

@@ -180,7 +180,7 @@ struct yoda_ctx {
     GroupDesc *fw_gdesc = nullptr;
     PodS *fw_pods = nullptr;
     u32 *fw_lead = nullptr;  // [6][tiles of SCANT pods] leading-run maxima of the maxima scan
-    u32 *fw_m_sorted = nullptr, *fw_step = nullptr, *fw_cls_max = nullptr, *fw_tables = nullptr;
+    u32 *fw_m_sorted = nullptr, *fw_step = nullptr, *fw_cls_max = nullptr, *fw_cls_order = nullptr, *fw_tables = nullptr;
     u32 fw_tables_classes = 0;
     FastCtl *fw_ctl = nullptr, *fw_hctl = nullptr;
     u32 fw_n_groups = 0, fw_n_classes = 0;
@@ -395,7 +395,7 @@ extern "C" void yoda_destroy(yoda_ctx *c) {
     dev_free(c->fw_slot); dev_free(c->fw_keys_in); dev_free(c->fw_keys_out);
     dev_free(c->fw_vals_in); dev_free(c->fw_vals_out); dev_free(c->fw_gdesc); dev_free(c->fw_pods);
     dev_free(c->fw_lead);
-    dev_free(c->fw_m_sorted); dev_free(c->fw_step); dev_free(c->fw_cls_max); dev_free(c->fw_tables); dev_free(c->fw_ctl);
+    dev_free(c->fw_m_sorted); dev_free(c->fw_step); dev_free(c->fw_cls_max); dev_free(c->fw_cls_order); dev_free(c->fw_tables); dev_free(c->fw_ctl);
     dev_free(c->sq_alloc); dev_free(c->sq_stat); dev_free(c->sq_pos); dev_free(c->sq_order); dev_free(c->sq_status);
     if (c->fw_cub_tmp) cudaFree(c->fw_cub_tmp);
     if (c->fw_hctl) cudaFreeHost(c->fw_hctl);
@@ -665,6 +665,7 @@ static int ensure_fast(yoda_ctx *c, u32 P) {
         if (cudaMallocHost((void **)&c->fw_hctl, sizeof(FastCtl)) != cudaSuccess) return fail(YODA_E_NOMEM, "cudaMallocHost failed");
         TRY(dev_alloc(&c->fw_gdesc, FAST_GROUP_CAP));
         TRY(dev_alloc(&c->fw_cls_max, (size_t)FAST_CLASS_CAP * 6));
+        TRY(dev_alloc(&c->fw_cls_order, (size_t)FAST_CLASS_CAP));
     }
     if (P <= c->fw_pods_cap) return YODA_OK;
     CU(cudaStreamSynchronize(c->stream));
@@ -941,7 +942,7 @@ static int fast_classes(yoda_ctx *c) {
             c->fw_tables_classes = want;
         }
         if (N) {
-            k_class_tables<<<dim3((N + CLST - 1) / CLST, (P + CLS_PER - 1) / CLS_PER), CLST, 0, st>>>(c->snap, c->fw_cls_max, P, c->fw_tables, c->fw_ctl, false);
+            k_class_tables<<<dim3((N + CLST - 1) / CLST, (P + CLS_PER - 1) / CLS_PER), CLST, 0, st>>>(c->snap, c->fw_cls_max, P, c->fw_tables, c->fw_ctl, false, nullptr);
             LAUNCHED(c);
         }
         if (c->fw_allow_defer) {
@@ -971,8 +972,10 @@ static int fast_classes(yoda_ctx *c) {
         k_class_assign<<<pb, 256, 0, st>>>(c->fw_pods, P, c->d_max6, c->fw_crep, c->fw_cids, c->fw_slot, c->fw_cls_max, cap_now, c->fw_ctl);
         LAUNCHED(c);
         if (N) {
+            k_class_order<<<(cap_now * 32 + CLS_ORDER_T - 1) / CLS_ORDER_T, CLS_ORDER_T, 0, st>>>(c->fw_cls_max, cap_now, c->fw_ctl, true, c->fw_cls_order);
+            LAUNCHED(c);
             dim3 grid((N + CLST - 1) / CLST, (cap_now + CLS_PER - 1) / CLS_PER);
-            k_class_tables<<<grid, CLST, 0, st>>>(c->snap, c->fw_cls_max, cap_now, c->fw_tables, c->fw_ctl, true);
+            k_class_tables<<<grid, CLST, 0, st>>>(c->snap, c->fw_cls_max, cap_now, c->fw_tables, c->fw_ctl, true, c->fw_cls_order);
             LAUNCHED(c);
         }
         c->fw_optimistic = true;
@@ -1013,8 +1016,10 @@ static int fast_classes(yoda_ctx *c) {
         c->fw_tables_classes = want;
     }
     if (N) {
+        k_class_order<<<(c->fw_n_classes * 32 + CLS_ORDER_T - 1) / CLS_ORDER_T, CLS_ORDER_T, 0, st>>>(c->fw_cls_max, c->fw_n_classes, c->fw_ctl, false, c->fw_cls_order);
+        LAUNCHED(c);
         dim3 grid((N + CLST - 1) / CLST, (c->fw_n_classes + CLS_PER - 1) / CLS_PER);
-        k_class_tables<<<grid, CLST, 0, st>>>(c->snap, c->fw_cls_max, c->fw_n_classes, c->fw_tables, c->fw_ctl, false);
+        k_class_tables<<<grid, CLST, 0, st>>>(c->snap, c->fw_cls_max, c->fw_n_classes, c->fw_tables, c->fw_ctl, false, c->fw_cls_order);
         LAUNCHED(c);
     }
     if (c->fw_allow_defer) {
