@@ -46,14 +46,17 @@ var (
 )
 
 // Yoda keeps the node-name <-> device-index dictionary and the host mirror of what the device
-// holds per node.  mu guards every field below it: informer goroutines write under Lock, the 16
-// framework goroutines of a cycle read under RLock.
+// holds per node.  mu guards every field below it: informer goroutines and evaluations take it for
+// writing.  The per-node calls of a cycle (Filter / Score from the 16 framework goroutines) do not
+// take it: they read the cycle's memo, which pins the dictionary as it was at the evaluation.  The
+// dictionary is copied before a new name is added while a memo may still read it (indexPinned).
 type Yoda struct {
 	handle framework.Handle
 	dev    *b200.Ctx
 
-	mu      sync.RWMutex
-	index   map[string]uint32 // node name -> dense device index
+	mu          sync.RWMutex
+	index       map[string]uint32 // node name -> dense device index
+	indexPinned bool              // some cycle's memo holds `index`: copy before the next insert
 	names   []string
 	hasScv  []bool
 	reject  []string // why the node's last Scv was refused by the device ("" = accepted)
@@ -67,7 +70,8 @@ type Yoda struct {
 // later Filter/Score/NormalizeScore calls of the cycle never look at state an informer may be changing.
 type memo struct {
 	res    b200.PodResult
-	n      uint32   // nodes the evaluation covered; indices >= n were registered later
+	n      uint32            // nodes the evaluation covered; indices >= n were registered later
+	index  map[string]uint32 // the dictionary at evaluation time; never written while a memo holds it
 	has    []bool   // copy of hasScv[:n] at evaluation time
 	reject []string // copy of reject[:n]
 	bits   []uint32
@@ -152,6 +156,13 @@ func (y *Yoda) indexOfLocked(name string) uint32 {
 		return i
 	}
 	i := uint32(len(y.names))
+	if y.indexPinned { // a cycle still looks names up in the current map: leave it untouched
+		next := make(map[string]uint32, len(y.index)+1)
+		for k, v := range y.index {
+			next[k] = v
+		}
+		y.index, y.indexPinned = next, false
+	}
 	y.index[name] = i
 	y.names = append(y.names, name)
 	y.hasScv = append(y.hasScv, false)
@@ -160,13 +171,6 @@ func (y *Yoda) indexOfLocked(name string) uint32 {
 	y.gen = append(y.gen, 0)
 	y.genSeen = append(y.genSeen, false)
 	return i
-}
-
-func (y *Yoda) lookup(name string) (uint32, bool) {
-	y.mu.RLock()
-	i, ok := y.index[name]
-	y.mu.RUnlock()
-	return i, ok
 }
 
 func (y *Yoda) onScv(s *scv.Scv) {
@@ -261,7 +265,8 @@ func (y *Yoda) cycle(state *framework.CycleState, pod *v1.Pod) (*memo, error) {
 	if int(n) > len(y.hasScv) {
 		n = uint32(len(y.hasScv))
 	}
-	m := &memo{res: res[0], n: n, bits: make([]uint32, (n+31)/32+1), raw: make([]int64, n+1), norm: make([]uint8, n+1)}
+	y.indexPinned = true
+	m := &memo{res: res[0], n: n, index: y.index, bits: make([]uint32, (n+31)/32+1), raw: make([]int64, n+1), norm: make([]uint8, n+1)}
 	m.has = append([]bool(nil), y.hasScv[:n]...)
 	m.reject = append([]string(nil), y.reject[:n]...)
 	if n > 0 {
@@ -287,7 +292,7 @@ func (y *Yoda) Filter(_ context.Context, state *framework.CycleState, pod *v1.Po
 	if err != nil {
 		return framework.NewStatus(framework.Error, err.Error())
 	}
-	i, ok := y.lookup(name)
+	i, ok := m.index[name]
 	if !ok || !m.known(i) {
 		why := notFound(name)
 		if ok && i < m.n && m.reject[i] != "" {
@@ -327,7 +332,7 @@ func (y *Yoda) Score(_ context.Context, state *framework.CycleState, p *v1.Pod, 
 	if err != nil {
 		return 0, framework.NewStatus(framework.Error, fmt.Sprintf("Score Node Error: %v", err))
 	}
-	i, ok := y.lookup(nodeName)
+	i, ok := m.index[nodeName]
 	if !ok || !m.known(i) { // scheduler.go:117-122; also a node registered after this cycle's evaluation
 		return 0, framework.NewStatus(framework.Error, "Score Node Error: "+notFound(nodeName))
 	}
@@ -353,15 +358,13 @@ func (y *Yoda) NormalizeScore(_ context.Context, state *framework.CycleState, _ 
 	own := m != nil && uint32(len(scores)) == b200.Feasible(&m.res)
 	idx := make([]uint32, len(scores))
 	if own {
-		y.mu.RLock()
 		for k := 0; own && k < len(scores); k++ {
-			i, ok := y.index[scores[k].Name]
+			i, ok := m.index[scores[k].Name]
 			// norm == 255 marks a rescale that wrapped outside [0,100]: the reference returns the wrapped int64,
 			// which only the exact list path below reproduces
 			own = ok && m.feasible(i) && m.raw[i] == scores[k].Score && m.norm[i] != 255
 			idx[k] = i
 		}
-		y.mu.RUnlock()
 	}
 	if own {
 		for k := range scores {

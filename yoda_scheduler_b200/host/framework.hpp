@@ -4,6 +4,7 @@
 // and the benchmark harness can run without a cluster ("fake framework handle").
 // Only what pkg/yoda/scheduler.go uses is here; names follow the Go originals.
 #pragma once
+#include <atomic>
 #include <cstdint>
 #include <map>
 #include <memory>
@@ -59,6 +60,10 @@ struct StateData {
 // framework.CycleState: per-scheduling-cycle key/value store with its own read/write lock (Go: sync.RWMutex)
 class CycleState {
    public:
+    CycleState() : serial_(next_serial().fetch_add(1, std::memory_order_relaxed) + 1) {}
+    // Identity of this cycle: unique per CycleState object for the life of the process (an address would be reused).
+    // Not part of the Go type; the C++ mirror uses it to remember, per thread, what it already looked up in this cycle.
+    uint64_t Serial() const { return serial_; }
     void Lock() { mu_.lock(); }
     void Unlock() { mu_.unlock(); }
     void RLock() { mu_.lock_shared(); }
@@ -68,8 +73,18 @@ class CycleState {
         auto it = data_.find(key);
         return it == data_.end() ? nullptr : it->second;
     }
+    // the same without taking a reference: the entry lives as long as the cycle state does
+    const StateData *Peek(const std::string &key) const {
+        auto it = data_.find(key);
+        return it == data_.end() ? nullptr : it->second.get();
+    }
 
    private:
+    static std::atomic<uint64_t> &next_serial() {
+        static std::atomic<uint64_t> n{0};
+        return n;
+    }
+    const uint64_t serial_;
     std::shared_mutex mu_;
     std::unordered_map<std::string, std::shared_ptr<StateData>> data_;
 };

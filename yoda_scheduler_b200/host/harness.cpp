@@ -11,6 +11,8 @@
 //       feasible node, NormalizeScore, selectHost (here: lowest index among the top scores);
 // and checks (2) against (1).  Exit code 0 = identical.  One JSON line on stdout.
 #include <chrono>
+#include <condition_variable>
+#include <mutex>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -32,6 +34,62 @@ struct FakeHandle : framework::Handle {
         auto it = infos.find(name);
         return it == infos.end() ? nullptr : &it->second;
     }
+};
+
+// A fixed set of worker threads handing out pieces of 64 indices, like parallelize.Until with its chunking.
+class Workers {
+   public:
+    explicit Workers(unsigned n) {
+        for (unsigned t = 0; t < n; ++t) pool_.emplace_back([this]() { loop(); });
+    }
+    ~Workers() {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            stop_ = true;
+            ++gen_;
+        }
+        cv_.notify_all();
+        for (auto &th : pool_) th.join();
+    }
+    void run(size_t n, const std::function<void(size_t)> &f) {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            n_ = n;
+            f_ = &f;
+            next_.store(0);
+            left_ = (unsigned)pool_.size();
+            ++gen_;
+        }
+        cv_.notify_all();
+        std::unique_lock<std::mutex> lk(mu_);
+        done_.wait(lk, [&]() { return left_ == 0; });
+    }
+
+   private:
+    void loop() {
+        uint64_t seen = 0;
+        for (;;) {
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&]() { return gen_ != seen; });
+                seen = gen_;
+                if (stop_) return;
+            }
+            for (size_t i = next_.fetch_add(64); i < n_; i = next_.fetch_add(64))
+                for (size_t k = i; k < std::min(n_, i + 64); ++k) (*f_)(k);
+            std::lock_guard<std::mutex> lk(mu_);
+            if (--left_ == 0) done_.notify_one();
+        }
+    }
+    std::vector<std::thread> pool_;
+    std::mutex mu_;
+    std::condition_variable cv_, done_;
+    std::atomic<size_t> next_{0};
+    size_t n_ = 0;
+    const std::function<void(size_t)> *f_ = nullptr;
+    unsigned left_ = 0;
+    uint64_t gen_ = 0;
+    bool stop_ = false;
 };
 
 static uint64_t fnv(uint64_t h, uint64_t v) {
@@ -123,16 +181,8 @@ int main(int argc, char **argv) {
     int mismatches = 0;
     cycles = std::min<uint64_t>(cycles, P);
     std::vector<double> cycle_times;
-    auto parallel_nodes = [&](size_t n, const std::function<void(size_t)> &f) {
-        std::atomic<size_t> next{0};
-        std::vector<std::thread> pool;
-        for (uint64_t t = 0; t < threads; ++t)
-            pool.emplace_back([&]() {
-                for (size_t i = next.fetch_add(64); i < n; i = next.fetch_add(64))
-                    for (size_t k = i; k < std::min(n, i + 64); ++k) f(k);
-            });
-        for (auto &th : pool) th.join();
-    };
+    Workers workers((unsigned)threads);  // kube-scheduler keeps its 16 workers too (parallelize.Until)
+    auto parallel_nodes = [&](size_t n, const std::function<void(size_t)> &f) { workers.run(n, f); };
     t0 = Clock::now();
     for (uint64_t p = 0; p < cycles; ++p) {
         const auto c0 = Clock::now();
@@ -142,9 +192,9 @@ int main(int argc, char **argv) {
         parallel_nodes(nodes.size(), [&](size_t n) {  // findNodesThatPassFilters
             fit[n] = plugin->Filter(state, pod, *handle.GetNodeInfo(nodes[n].scv.Name)).IsSuccess();
         });
-        std::vector<std::string> feasible;
+        std::vector<const std::string *> feasible;
         for (size_t n = 0; n < nodes.size(); ++n)
-            if (fit[n]) feasible.push_back(nodes[n].scv.Name);
+            if (fit[n]) feasible.push_back(&nodes[n].scv.Name);
         auto pf = plugin->PostFilter(state, pod);  // max-collection hook
         if (!pf.second.IsSuccess()) { mismatches++; continue; }
         int32_t chosen = -1;
@@ -152,12 +202,16 @@ int main(int argc, char **argv) {
             framework::NodeScoreList scores(feasible.size());
             std::atomic<int> bad{0};
             parallel_nodes(feasible.size(), [&](size_t k) {  // RunScorePlugins
-                auto sc = plugin->Score(state, pod, feasible[k]);
+                auto sc = plugin->Score(state, pod, *feasible[k]);
                 if (!sc.second.IsSuccess()) bad++;
-                scores[k] = {feasible[k], sc.first};
+                scores[k] = {*feasible[k], sc.first};
             });
             mismatches += bad.load();
+            // odd cycles hand the list over back to front: NormalizeScore must not depend on the order it comes in
+            // (in node order it matches names against the feasible bits, otherwise it looks every name up)
+            if (p & 1) std::reverse(scores.begin(), scores.end());
             plugin->NormalizeScore(state, pod, scores);
+            if (p & 1) std::reverse(scores.begin(), scores.end());
             int64_t best = -1;
             for (const auto &s : scores)  // selectHost with the deterministic tie-break of the harness
                 if (s.Score > best) { best = s.Score; chosen = plugin->NodeIndex(s.Name); }

@@ -70,10 +70,11 @@ std::unique_ptr<Yoda> Yoda::New(const Options &opt, const framework::Handle *h, 
 Yoda::~Yoda() { yoda_destroy(ctx_); }
 
 uint32_t Yoda::index_of(const std::string &name) {
-    auto it = index_.find(name);
-    if (it != index_.end()) return it->second;
+    auto it = index_->find(name);
+    if (it != index_->end()) return it->second;
     const uint32_t idx = (uint32_t)names_.size();
-    index_.emplace(name, idx);
+    if (index_.use_count() > 1) index_ = std::make_shared<IndexMap>(*index_);  // a cycle's memo still reads the old one
+    index_->emplace(name, idx);
     names_.push_back(name);
     has_scv_.push_back(0);
     reject_.emplace_back();
@@ -82,8 +83,8 @@ uint32_t Yoda::index_of(const std::string &name) {
 }
 int32_t Yoda::NodeIndex(const std::string &name) const {
     std::shared_lock<std::shared_mutex> lk(mu_);
-    auto it = index_.find(name);
-    return it == index_.end() ? -1 : (int32_t)it->second;
+    auto it = index_->find(name);
+    return it == index_->end() ? -1 : (int32_t)it->second;
 }
 
 // ---- informer events ---------------------------------------------------------------------------
@@ -100,6 +101,7 @@ Status Yoda::OnScvUpsert(const scv::Scv &s) {
     auto refuse = [&](const std::string &why) {
         yoda_node_remove(ctx_, idx);
         has_scv_[idx] = 0;
+        n_rejected_ += reject_[idx].empty() ? 1 : 0;
         reject_[idx] = why;
         dirty_ = true;
         return NewStatus(framework::Error, why);
@@ -117,6 +119,7 @@ Status Yoda::OnScvUpsert(const scv::Scv &s) {
     }
     if (yoda_node_upsert(ctx_, idx, &rec) != YODA_OK) return refuse(yoda_last_error());
     has_scv_[idx] = 1;
+    n_rejected_ -= reject_[idx].empty() ? 0 : 1;
     reject_[idx].clear();
     dirty_ = true;
     return NewStatus(framework::Success);
@@ -126,6 +129,7 @@ void Yoda::OnScvDelete(const std::string &nodeName) {
     const uint32_t idx = index_of(nodeName);
     yoda_node_remove(ctx_, idx);
     has_scv_[idx] = 0;
+    n_rejected_ -= reject_[idx].empty() ? 0 : 1;
     reject_[idx].clear();
     dirty_ = true;
 }
@@ -171,7 +175,16 @@ struct Yoda::Memo : framework::StateData {
     yoda_pod_result res{};
     uint32_t n_nodes = 0;            // nodes the evaluation covered; indices >= n_nodes were registered later
     std::vector<uint8_t> has;        // has_scv_[0..n_nodes) as of the evaluation: the cycle's frozen view
-    std::vector<std::string> reject;
+    std::shared_ptr<const IndexMap> index;  // name -> index as of the evaluation (never modified while pinned here)
+    int32_t index_of(const std::string &name) const {
+        auto it = index->find(name);
+        return it == index->end() ? -1 : (int32_t)it->second;
+    }
+    std::unordered_map<uint32_t, std::string> reject;  // nodes whose last Scv was refused, and why (usually none)
+    const std::string *rejected(uint32_t idx) const {
+        auto it = reject.find(idx);
+        return it == reject.end() ? nullptr : &it->second;
+    }
     std::vector<uint32_t> bits;
     std::vector<int64_t> raw;
     std::vector<uint8_t> norm;
@@ -182,13 +195,31 @@ static const char *kMemoKey = "yoda/b200";
 
 // First plugin call of a cycle evaluates the pod against every node once (one device pass) and
 // stores the rows in CycleState under the state lock, as collection.go:53-55 does for "Max".
-std::shared_ptr<Yoda::Memo> Yoda::memo(framework::CycleState &state, const v1::Pod &pod, Status *st) {
-    state.RLock();  // every call after the first of a cycle: a shared read, 16 framework threads at once
-    auto have = std::dynamic_pointer_cast<Memo>(state.Read(kMemoKey));
+// What a thread already found in a cycle: the per-node calls of one cycle come in runs on the same thread (Filter on
+// thousands of nodes), and the cycle's entries never change once written, so only the first call of a run takes the
+// state's read lock -- sixteen threads taking it per node would spend their time passing its cache line around.
+namespace {
+struct CycleSeen {
+    uint64_t serial = 0;
+    const void *memo = nullptr;
+    bool have_max = false;
+};
+thread_local CycleSeen t_seen;
+}  // namespace
+
+const Yoda::Memo *Yoda::memo(framework::CycleState &state, const v1::Pod &pod, Status *st) {
+    if (t_seen.serial == state.Serial() && t_seen.memo) return static_cast<const Memo *>(t_seen.memo);
+    auto remember = [&](const Memo *m) {
+        if (t_seen.serial != state.Serial()) t_seen = CycleSeen{state.Serial(), nullptr, false};
+        t_seen.memo = m;
+        return m;
+    };
+    state.RLock();
+    const Memo *have = dynamic_cast<const Memo *>(state.Peek(kMemoKey));
     state.RUnlock();
-    if (have) return have;
+    if (have) return remember(have);
     state.Lock();
-    have = std::dynamic_pointer_cast<Memo>(state.Read(kMemoKey));
+    have = dynamic_cast<const Memo *>(state.Peek(kMemoKey));
     if (!have) {
         std::unique_lock<std::shared_mutex> lk(mu_);
         Status s = sync_locked();
@@ -201,8 +232,11 @@ std::shared_ptr<Yoda::Memo> Yoda::memo(framework::CycleState &state, const v1::P
             } else {
                 n = std::min<uint32_t>(n, (uint32_t)has_scv_.size());
                 m->n_nodes = n;
+                m->index = index_;
                 m->has.assign(has_scv_.begin(), has_scv_.begin() + n);
-                m->reject.assign(reject_.begin(), reject_.begin() + n);
+                if (n_rejected_)
+                    for (uint32_t i = 0; i < n; ++i)
+                        if (!reject_[i].empty()) m->reject.emplace(i, reject_[i]);
                 m->bits.assign((n + 31) / 32 + 1, 0);
                 m->raw.assign(n + 1, 0);
                 m->norm.assign(n + 1, 0);
@@ -212,13 +246,13 @@ std::shared_ptr<Yoda::Memo> Yoda::memo(framework::CycleState &state, const v1::P
         }
         if (s.IsSuccess()) {
             state.Write(kMemoKey, m);
-            have = m;
+            have = m.get();
         } else if (st) {
             *st = s;
         }
     }
     state.Unlock();
-    return have;
+    return have ? remember(have) : nullptr;
 }
 
 // ---- plugin methods ----------------------------------------------------------------------------
@@ -226,12 +260,12 @@ std::shared_ptr<Yoda::Memo> Yoda::memo(framework::CycleState &state, const v1::P
 Status Yoda::Filter(framework::CycleState &state, const v1::Pod &pod, const framework::NodeInfo &node) {
     const std::string &name = node.Node().Name;
     Status st;
-    auto m = memo(state, pod, &st);
+    const Memo *m = memo(state, pod, &st);
     if (!m) return st;
-    const int32_t idx = NodeIndex(name);
+    const int32_t idx = m->index_of(name);
     if (!m->known(idx)) {  // cache.Get failed (:81-84); also a node registered after this cycle's evaluation
-        if (idx >= 0 && (uint32_t)idx < m->n_nodes && !m->reject[idx].empty())
-            return NewStatus(framework::Unschedulable, "Node:" + name + " Scv rejected: " + m->reject[idx]);
+        const std::string *why = (idx >= 0 && (uint32_t)idx < m->n_nodes) ? m->rejected((uint32_t)idx) : nullptr;
+        if (why) return NewStatus(framework::Unschedulable, "Node:" + name + " Scv rejected: " + *why);
         return NewStatus(framework::Unschedulable, "Node:" + name + " Scv.core.run-linux.com \"" + name + "\" not found");
     }
     if (m->feasible((uint32_t)idx)) return NewStatus(framework::Success, "");
@@ -241,7 +275,7 @@ Status Yoda::Filter(framework::CycleState &state, const v1::Pod &pod, const fram
 // scheduler.go:95-103 + collection.go:30-57: publishes collection.Data under "Max"
 std::pair<framework::PostFilterResult, Status> Yoda::PostFilter(framework::CycleState &state, const v1::Pod &pod) {
     Status st;
-    auto m = memo(state, pod, &st);
+    const Memo *m = memo(state, pod, &st);
     if (!m) return {framework::PostFilterResult{}, st.code == framework::Success ? NewStatus(framework::Error, "evaluation failed") : st};
     auto d = std::make_shared<Data>();
     d->Value.MaxBandwidth = m->res.max_bandwidth;
@@ -265,14 +299,18 @@ std::pair<int64_t, Status> Yoda::Score(framework::CycleState &state, const v1::P
     if (!handle_ || !handle_->GetNodeInfo(nodeName))  // :111-114
         return {0, NewStatus(framework::Error, "getting node \"" + nodeName + "\" from Snapshot: nodeinfo not found for node name \"" + nodeName + "\"")};
     Status st;
-    auto m = memo(state, p, &st);
+    const Memo *m = memo(state, p, &st);
     if (!m) return {0, NewStatus(framework::Error, "Score Node Error: " + st.message)};
-    const int32_t idx = NodeIndex(nodeName);
+    const int32_t idx = m->index_of(nodeName);
     if (!m->known(idx))  // :117-122; a node registered after the cycle's evaluation is not part of it either
         return {0, NewStatus(framework::Error, "Score Node Error: Scv.core.run-linux.com \"" + nodeName + "\" not found")};
-    state.RLock();
-    const bool have_max = std::dynamic_pointer_cast<Data>(state.Read("Max")) != nullptr;
-    state.RUnlock();
+    bool have_max = t_seen.serial == state.Serial() && t_seen.have_max;  // once written it stays for the cycle
+    if (!have_max) {
+        state.RLock();
+        have_max = dynamic_cast<const Data *>(state.Peek("Max")) != nullptr;
+        state.RUnlock();
+        if (t_seen.serial == state.Serial()) t_seen.have_max = have_max;
+    }
     if (!have_max)  // algorithm.go:29-37: "Max" must have been written
         return {0, NewStatus(framework::Error, "Score Node Error: not found")};
     return {m->raw[idx], NewStatus(framework::Success, "")};
@@ -284,12 +322,27 @@ std::pair<int64_t, Status> Yoda::Score(framework::CycleState &state, const v1::P
 Status Yoda::NormalizeScore(framework::CycleState &state, const v1::Pod &pod, framework::NodeScoreList &scores) {
     if (scores.empty()) throw std::out_of_range("index out of range [0] with length 0");  // scores[0], :135
     state.RLock();
-    auto m = std::dynamic_pointer_cast<Memo>(state.Read(kMemoKey));
+    const Memo *m = dynamic_cast<const Memo *>(state.Peek(kMemoKey));
     state.RUnlock();
     bool own = m && scores.size() == m->res.feasible;
     std::vector<int32_t> idx(scores.size(), -1);
+    if (own) {
+        // A list in node-index order (what a framework that filters in index order hands over) is matched against the
+        // feasible bits by comparing names, which is cheaper than hashing them; anything else is looked up by name.
+        std::shared_lock<std::shared_mutex> lk(mu_);  // names_ (indices below m->n_nodes never change their name)
+        size_t i = 0;
+        bool in_order = true;
+        for (uint32_t w = 0; in_order && w * 32 < m->n_nodes && i < scores.size(); ++w)
+            for (uint32_t word = m->bits[w]; word && i < scores.size(); word &= word - 1) {
+                const uint32_t n = w * 32 + (uint32_t)__builtin_ctz(word);
+                in_order = n < m->n_nodes && names_[n] == scores[i].Name;
+                if (!in_order) break;
+                idx[i++] = (int32_t)n;
+            }
+        if (!in_order || i != scores.size()) std::fill(idx.begin(), idx.end(), -1);
+    }
     for (size_t i = 0; own && i < scores.size(); ++i) {
-        idx[i] = NodeIndex(scores[i].Name);
+        if (idx[i] < 0) idx[i] = m->index_of(scores[i].Name);
         // norm == 255 marks a rescale that wrapped outside [0,100]: only the exact list path returns the wrapped int64
         own = idx[i] >= 0 && m->feasible((uint32_t)idx[i]) && m->raw[idx[i]] == scores[i].Score && m->norm[idx[i]] != 255;
     }

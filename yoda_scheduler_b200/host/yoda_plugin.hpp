@@ -73,18 +73,22 @@ class Yoda {
    private:
     Yoda() = default;
     struct Memo;  // per-cycle memo kept in CycleState
-    std::shared_ptr<Memo> memo(framework::CycleState &state, const v1::Pod &pod, framework::Status *st);
+    const Memo *memo(framework::CycleState &state, const v1::Pod &pod, framework::Status *st);
     uint32_t index_of(const std::string &name);
+    using IndexMap = std::unordered_map<std::string, uint32_t>;
 
     const framework::Handle *handle_ = nullptr;
     yoda_ctx *ctx_ = nullptr;
-    // mu_ guards everything below: event handlers and evaluations take it exclusively, the per-node lookups of
-    // Filter / Score / NormalizeScore (16 framework threads at once) take it shared
+    // mu_ guards everything below: event handlers and evaluations take it exclusively.  The per-node calls of a cycle
+    // (Filter / Score from 16 framework threads at once) do not take it at all: they read the cycle's memo, which
+    // pins the name -> index map as it was at the evaluation.  The map is copied before a new node is added to it
+    // while some memo still pins it, and changed in place otherwise.
     mutable std::shared_mutex mu_;
-    std::unordered_map<std::string, uint32_t> index_;
+    std::shared_ptr<IndexMap> index_ = std::make_shared<IndexMap>();
     std::vector<std::string> names_;
     std::vector<uint8_t> has_scv_;
     std::vector<std::string> reject_;  // why the node's last Scv was refused ("" = accepted)
+    uint32_t n_rejected_ = 0;          // non-empty entries of reject_
     std::vector<uint64_t> alloc_;
     bool dirty_ = false;
     framework::Status sync_locked();
