@@ -69,7 +69,7 @@ __device__ __forceinline__ void load8(const u32 *p, u32 *dst) {
 __device__ __forceinline__ u32 hash_insert(u64 *keys, u32 mask, u64 key) {
     u32 slot = (u32)mix64(key) & mask;
     for (;;) {
-        u64 cur = keys[slot];
+        u64 cur = __ldcg(&keys[slot]);  // from L2: a key another SM has just published is seen, and no atomic is needed for it
         if (cur == key) return slot;
         if (cur == HASH_EMPTY) {
             cur = atomicCAS(&keys[slot], HASH_EMPTY, key);
@@ -108,12 +108,17 @@ __device__ __forceinline__ u64 group_key(const PodC &p, u32 &num32, u32 &c32, u3
     return (u64)num32;
 }
 
+// A batch has far fewer groups (and classes) than pods: a thread per pod would send the whole batch into compare-and-swaps
+// on a hundred addresses at the same instant.  INSERT_PER pods per thread, one after the other: only the first round finds
+// empty slots, the later ones read the published keys.
+#define INSERT_PER 8
 __global__ void k_group_insert(const PodC *__restrict__ pods, u32 P, u64 *gkeys, u32 gmask, u32 *slot_of_pod) {
-    u32 p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= P) return;
-    u32 n32, c32, gf;
-    const u64 key = group_key(pods[p], n32, c32, gf);
-    slot_of_pod[p] = hash_insert(gkeys, gmask, key);
+    const u32 stride = gridDim.x * blockDim.x;
+    for (u32 p = blockIdx.x * blockDim.x + threadIdx.x; p < P; p += stride) {
+        u32 n32, c32, gf;
+        const u64 key = group_key(pods[p], n32, c32, gf);
+        slot_of_pod[p] = hash_insert(gkeys, gmask, key);
+    }
 }
 
 // pod -> gid, sort key (has-clock | gid | memory), group descriptor
@@ -434,12 +439,13 @@ __device__ __forceinline__ u64 class_hash(const u64 *mx) {
 }
 __global__ void k_class_insert(const PodS *__restrict__ pods, u32 P, const u64 *__restrict__ max6, u64 *ckeys, u32 cmask, u32 *rep,
                                u32 *slot_of_pod) {
+    // (a thread per pod here: the six maxima of a pod are a scattered 48-byte read, which wants all the threads it can get)
     u32 i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P) return;
     const u32 orig = pods[i].orig;
     const u32 slot = hash_insert(ckeys, cmask, class_hash(max6 + (size_t)orig * 6));
     slot_of_pod[i] = slot;
-    if (rep[slot] > orig) atomicMin(&rep[slot], orig);  // a deterministic representative pod
+    if (__ldcg(&rep[slot]) > orig) atomicMin(&rep[slot], orig);  // a deterministic representative pod
 }
 // pod -> class id; verify the tuple against the representative's (hash collisions -> error flag);
 // the representative records the class maxima

@@ -827,7 +827,7 @@ static int fast_phase0(yoda_ctx *c) {
     }
     k_hash_clear<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_gkeys, c->fw_gids, c->fw_htab);
     LAUNCHED(c);
-    k_group_insert<<<pb, 256, 0, st>>>(c->d_pods, P, c->fw_gkeys, c->fw_htab - 1, c->fw_slot);
+    k_group_insert<<<(pb + INSERT_PER - 1) / INSERT_PER, 256, 0, st>>>(c->d_pods, P, c->fw_gkeys, c->fw_htab - 1, c->fw_slot);
     LAUNCHED(c);
     k_hash_compact<<<(c->fw_htab + 255) / 256, 256, 0, st>>>(c->fw_gkeys, c->fw_gids, c->fw_htab, &c->fw_ctl->n_groups);
     LAUNCHED(c);
