@@ -679,8 +679,8 @@ __global__ void __launch_bounds__(CLST) k_class_tables(DevSnap s, const u32 *__r
 #define HOT_WARPS (HOT_THREADS / 32)
 #define HOT_CHUNK 128  // pods per CTA of the output pass
 #ifndef SCORE_CHUNK
-#define SCORE_CHUNK 192  // pods per CTA of the score pass: every chunk starts with a full evaluation of the CTA's nodes
-                         // (192 keeps the CTA's shared memory near 52 KB: four CTAs per SM; measured best of 128/192/256)
+#define SCORE_CHUNK 256  // pods per CTA of the score pass: every chunk starts with a full evaluation of the CTA's nodes
+                         // (measured best of 160/192/256/320; ~43 KB of shared memory per CTA, four CTAs per SM)
 #endif
 
 template <int NPL>
@@ -817,10 +817,10 @@ __device__ __forceinline__ void half_sync(int bar_id) { asm volatile("bar.sync %
 #define SCORE_BLK 4  // chunk sizes stay multiples of this (hot_chunk in runtime.cu)
 template <int NPL, bool DECIDE>
 struct ScoreSmem {
-    // the CTA's nodes, resident for the whole chunk: FreeMemory of the eight card slots, and the card contributions of the
-    // current (group, class) run with the group's clock tests folded in (as hot_load_class does for the output pass);
-    // [half][node]: consecutive lanes read consecutive 16-byte pieces
-    uint4 fr[2][HOT_WARPS * NPL * 32];
+    // the card contributions of the CTA's nodes for the current (group, class) run, with the group's clock tests folded in
+    // (as hot_load_class does for the output pass); [half][node]: consecutive lanes read consecutive 16-byte pieces.
+    // (The nodes' FreeMemory values stay in registers: the pass is bound by the shared-memory/LSU data path -- 75 % of its
+    // wavefront peak with both in shared memory -- and the 16 registers still fit four CTAs per SM; score phase -5 %.)
     uint4 cs[2][HOT_WARPS * NPL * 32];
     uint4 sp[SCORE_CHUNK * 2];
     u32 m_s[SCORE_CHUNK];    // memory value of every pod of the chunk (ascending inside a run)
@@ -834,8 +834,9 @@ struct ScoreSmem {
 };
 
 // score reduce: lowest / highest over the feasible nodes of every pod (scheduler.go:134-145).
-// The nodes' FreeMemory values and their contributions for the current run live in shared memory, so re-evaluating a
-// slot inside a run touches no global memory at all; only a run change fetches class-table entries (and clocks) from L2.
+// The nodes' FreeMemory values live in registers and their contributions for the current run in shared memory, so
+// re-evaluating a slot inside a run touches no global memory at all; only a run change fetches class-table entries (and
+// clocks) from L2.
 // A warp does not walk the pods one by one.  After it has evaluated its nodes for pod i, everything it knows
 // stays valid up to the first later pod that either starts another (group, class) run or asks for more memory than
 // the smallest validity bound among its nodes -- and because the memory values ascend inside a run, that pod is
@@ -862,6 +863,7 @@ __device__ __forceinline__ void score_body(ScoreSmem<NPL, DECIDE> &sm, int bar_i
     const u32 base = (tile * HOT_WARPS + warp) * (NPL * 32);
     u32 node[NPL], cardnum[NPL], stat[NPL];
     bool ok[NPL], clkok[NPL];
+    uint4 frv[NPL][2];  // FreeMemory of the node's eight card slots
 #pragma unroll
     for (int j = 0; j < NPL; ++j) {
         const u32 n = base + j * 32 + lane;
@@ -872,9 +874,8 @@ __device__ __forceinline__ void score_body(ScoreSmem<NPL, DECIDE> &sm, int bar_i
         ok[j] = in && meta_table_node(s.meta[node[j]]);
         clkok[j] = true;
         const uint4 *src = reinterpret_cast<const uint4 *>(s.n32[F_FREE] + (size_t)node[j] * G);
-        const u32 slot = (warp * NPL + j) * 32 + lane;  // only this lane ever touches the slot: no barrier needed for it
-        sm.fr[0][slot] = src[0];
-        sm.fr[1][slot] = src[1];
+        frv[j][0] = src[0];
+        frv[j][1] = src[1];
     }
     half_sync(bar_id);
     u32 cur_key = 0xFFFFFFFFu;
@@ -908,7 +909,7 @@ __device__ __forceinline__ void score_body(ScoreSmem<NPL, DECIDE> &sm, int bar_i
                 sm.cs[1][slot] = make_uint4(cs[4], cs[5], cs[6], cs[7]);
             }
             if (!same || __any_sync(0xFFFFFFFFu, pod.m > bound[j])) {
-                const uint4 f0 = sm.fr[0][slot], f1 = sm.fr[1][slot], c0 = sm.cs[0][slot], c1 = sm.cs[1][slot];
+                const uint4 f0 = frv[j][0], f1 = frv[j][1], c0 = sm.cs[0][slot], c1 = sm.cs[1][slot];  // (the slot's cs entries: written by this lane only)
                 const u32 fr[G] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
                 const u32 cs[G] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
                 u32 acc = 0, b = 0xFFFFFFFFu;
@@ -1173,7 +1174,7 @@ __device__ __forceinline__ void out_body(OutSmem &sm, int bar_id, u32 tid, u32 t
 }
 
 #ifndef SCORE_MINB
-#define SCORE_MINB 4  // resident CTAs per SM the score pass is compiled for (its ~52 KB of shared memory allow four)
+#define SCORE_MINB 4  // resident CTAs per SM the score pass is compiled for (62 registers, ~43 KB of shared memory)
 #endif
 template <int NPL, bool DECIDE>
 __global__ void __launch_bounds__(HOT_THREADS, SCORE_MINB) k_fast_score(DevSnap s, const PodS *__restrict__ pods, u32 p_begin, u32 p_end,
